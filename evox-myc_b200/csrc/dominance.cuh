@@ -1,0 +1,194 @@
+// K0/K1: objective transpose and the tiled pairwise-dominance build.
+//
+// Replaces src/evox/utils/common.py:95-104 (`_dominate`, `dominate_relation`) as called at
+// src/evox/operators/selection/non_dominate.py:60 of the reference.  The reference materialises
+// an (N, N) byte matrix; here row i of the matrix is a run of 32-bit words, bit (j & 31) of word
+// (j >> 5) = "i dominates j".
+#pragma once
+
+#include "common.cuh"
+
+namespace evoxb {
+
+// ---- K0: (n, m) row-major -> (m, npad) objective-major, padded with NaN --------------------
+// NaN padding makes every compare against a padding column false, so padding bits are 0.
+__global__ void transpose_pad_kernel(const float *__restrict__ x, int64_t n, int m, int64_t npad,
+                                     float *__restrict__ xt) {
+    const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (j >= npad) return;
+    const float nanv = __int_as_float(0x7fc00000);
+    for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + j] = (j < n) ? x[j * m + k] : nanv;
+}
+
+// ---- K1: dominance tile -----------------------------------------------------------------------
+// CTA = 256 threads = 8 warps.  The CTA owns kTileRows rows x 1024 columns.  Warp w owns the 128
+// columns [w*128, w*128+128): lane l keeps objective vectors of columns l, l+32, l+64, l+96 in
+// registers (kC = 4 ballot words per row).  Rows are read from shared memory as warp-uniform
+// broadcasts.  For row i and column word c the 32 lanes evaluate the predicate and
+// __ballot_sync packs them; lane (i & 31) keeps the word, so after 32 rows every lane holds the
+// four words of one row and stores them as a single 16-byte vector.
+constexpr int kBuildThreads = 256;
+constexpr int kTileRows = 128;
+constexpr int kC = 4;
+constexpr int kTileCols = (kBuildThreads / 32) * kC * 32;  // 1024
+
+template <int M>
+__device__ __forceinline__ bool dominates(const float (&a)[M], const float (&b)[M]) {
+    // all(a <= b) & any(a < b) -- utils/common.py:98.  IEEE compares: NaN => false.
+    bool lt = false;
+#pragma unroll
+    for (int k = 0; k < M; ++k) lt = lt || (a[k] < b[k]);
+    bool p = lt;
+#pragma unroll
+    for (int k = 0; k < M; ++k) p = p && (a[k] <= b[k]);
+    return p;
+}
+
+template <int M>
+__global__ void __launch_bounds__(kBuildThreads)
+dominance_build_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows, int64_t row0,
+                       uint32_t *__restrict__ D, int64_t row_words) {
+    // xs[r][k]: objective vectors of the tile's rows
+    __shared__ float xs[kTileRows][M];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int64_t col_base = (int64_t)blockIdx.x * kTileCols + warp * (kC * 32);
+    const int64_t tile_row0 = (int64_t)blockIdx.y * kTileRows;  // local row index (0-based in this shard)
+
+    for (int t = threadIdx.x; t < kTileRows * M; t += kBuildThreads) {
+        const int r = t / M, k = t - r * M;
+        const int64_t gi = row0 + tile_row0 + r;  // global row index into xt
+        xs[r][k] = (tile_row0 + r < n_rows) ? xt[(int64_t)k * npad + gi] : __int_as_float(0x7fc00000);
+    }
+    float xj[kC][M];
+#pragma unroll
+    for (int c = 0; c < kC; ++c)
+#pragma unroll
+        for (int k = 0; k < M; ++k) xj[c][k] = xt[(int64_t)k * npad + col_base + c * 32 + lane];
+    __syncthreads();
+
+    for (int rb = 0; rb < kTileRows; rb += 32) {
+        uint32_t w[kC];
+#pragma unroll
+        for (int c = 0; c < kC; ++c) w[c] = 0u;
+#pragma unroll
+        for (int ii = 0; ii < 32; ++ii) {
+            float xi[M];
+#pragma unroll
+            for (int k = 0; k < M; ++k) xi[k] = xs[rb + ii][k];
+            const bool mine = (lane == ii);
+#pragma unroll
+            for (int c = 0; c < kC; ++c) {
+                const uint32_t b = __ballot_sync(0xffffffffu, dominates<M>(xi, xj[c]));
+                if (mine) w[c] = b;
+            }
+        }
+        const int64_t r = tile_row0 + rb + lane;
+        if (r < n_rows) {
+            uint4 v = make_uint4(w[0], w[1], w[2], w[3]);
+            *reinterpret_cast<uint4 *>(D + r * row_words + (col_base >> 5)) = v;
+        }
+    }
+}
+
+// Generic-M fallback (M > 12): same tiling, objectives looped at run time from shared memory.
+__global__ void __launch_bounds__(kBuildThreads)
+dominance_build_generic_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows, int64_t row0,
+                               int m, uint32_t *__restrict__ D, int64_t row_words) {
+    extern __shared__ float sm[];  // rows: kTileRows*m, then cols: kTileCols*m (objective-major)
+    float *xs = sm;
+    float *cs = sm + kTileRows * m;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int64_t tile_col0 = (int64_t)blockIdx.x * kTileCols;
+    const int64_t tile_row0 = (int64_t)blockIdx.y * kTileRows;
+    for (int t = threadIdx.x; t < kTileRows * m; t += kBuildThreads) {
+        const int r = t / m, k = t - r * m;
+        xs[t] = (tile_row0 + r < n_rows) ? xt[(int64_t)k * npad + row0 + tile_row0 + r] : __int_as_float(0x7fc00000);
+    }
+    for (int t = threadIdx.x; t < kTileCols * m; t += kBuildThreads) {
+        const int k = t / kTileCols, j = t - k * kTileCols;
+        cs[t] = xt[(int64_t)k * npad + tile_col0 + j];
+    }
+    __syncthreads();
+    for (int rb = 0; rb < kTileRows; rb += 32) {
+        uint32_t w[kC] = {0u, 0u, 0u, 0u};
+        for (int ii = 0; ii < 32; ++ii) {
+            const float *xi = xs + (rb + ii) * m;
+#pragma unroll
+            for (int c = 0; c < kC; ++c) {
+                const int j = warp * (kC * 32) + c * 32 + lane;
+                bool le = true, lt = false;
+                for (int k = 0; k < m; ++k) {
+                    const float a = xi[k], b = cs[k * kTileCols + j];
+                    le = le && (a <= b);
+                    lt = lt || (a < b);
+                }
+                const uint32_t b = __ballot_sync(0xffffffffu, le && lt);
+                if (lane == ii) w[c] = b;
+            }
+        }
+        const int64_t r = tile_row0 + rb + lane;
+        if (r < n_rows)
+            *reinterpret_cast<uint4 *>(D + r * row_words + ((tile_col0 + warp * (kC * 32)) >> 5)) =
+                make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// Launches K1 for rows [row0, row0 + n_rows) of the population against all npad columns.
+inline int launch_dominance_build(const float *xt, int64_t npad, int64_t row0, int64_t n_rows, int m,
+                                  uint32_t *D, int64_t row_words, cudaStream_t s) {
+    if (n_rows <= 0) return 0;
+    dim3 grid((unsigned)(npad / kTileCols), (unsigned)div_up(n_rows, kTileRows));
+    if (grid.y > 65535u) return fail(EVOXB_E_UNSUPPORTED, "too many row tiles (%u)", grid.y);
+#define EVOXB_BUILD_CASE(MM)                                                                           \
+    case MM:                                                                                           \
+        dominance_build_kernel<MM><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, row0, D, row_words); \
+        break;
+    switch (m) {
+        EVOXB_BUILD_CASE(1)
+        EVOXB_BUILD_CASE(2)
+        EVOXB_BUILD_CASE(3)
+        EVOXB_BUILD_CASE(4)
+        EVOXB_BUILD_CASE(5)
+        EVOXB_BUILD_CASE(6)
+        EVOXB_BUILD_CASE(7)
+        EVOXB_BUILD_CASE(8)
+        EVOXB_BUILD_CASE(9)
+        EVOXB_BUILD_CASE(10)
+        EVOXB_BUILD_CASE(11)
+        EVOXB_BUILD_CASE(12)
+        default: {
+            const size_t smem = sizeof(float) * (size_t)(kTileRows + kTileCols) * (size_t)m;
+            static thread_local size_t configured = 0;
+            if (smem > 48 * 1024 && smem > configured) {
+                EVOXB_CUDA(cudaFuncSetAttribute(dominance_build_generic_kernel,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                configured = smem;
+            }
+            dominance_build_generic_kernel<<<grid, kBuildThreads, smem, s>>>(xt, npad, n_rows, row0, m, D, row_words);
+        }
+    }
+#undef EVOXB_BUILD_CASE
+    EVOXB_LAUNCH_CHECK("dominance_build_kernel");
+    return 0;
+}
+
+// ---- a2: dense boolean relation between two different sets (utils/common.py:101-104) ----------
+// One thread per output byte, x row kept in registers via shared memory; small helper, not on the
+// N^2 hot path (the hot path never materialises bytes).
+__global__ void dominate_relation_dense_kernel(const float *__restrict__ x, int64_t nx, const float *__restrict__ y,
+                                               int64_t ny, int m, uint8_t *__restrict__ out) {
+    const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t i = blockIdx.y;
+    if (j >= ny || i >= nx) return;
+    bool le = true, lt = false;
+    for (int k = 0; k < m; ++k) {
+        const float a = x[i * m + k], b = y[j * m + k];
+        le = le && (a <= b);
+        lt = lt || (a < b);
+    }
+    out[i * ny + j] = (le && lt) ? 1 : 0;
+}
+
+}  // namespace evoxb

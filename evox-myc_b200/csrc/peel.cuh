@@ -1,0 +1,254 @@
+// K2/K3: dominator counts and the front-peeling loop over the bit-packed dominance matrix.
+//
+// Replaces src/evox/operators/selection/non_dominate.py:61 (dominate_count = sum(D, axis=0)) and
+// the while_loop at :72-111 (same loop as host_rank_from_domination_matrix, :11-27) of the
+// reference.  The reference's GPU formulation re-reads the whole N x N byte matrix once per front;
+// here the packed row of every individual is streamed exactly once, when it enters a front.
+//
+// Column sums over a set of packed rows are a "positional popcount": every lane keeps bit-sliced
+// (vertical) counters for the words it owns and feeds them through a carry-save-adder tree, so
+// counting costs a few LOP3 per 32 pairs instead of one add per pair.  The eight warps of a CTA
+// then add their bit-sliced counters in shared memory, expand them once to integers and apply
+// them to count[] with one atomicAdd per touched column.
+#pragma once
+
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+
+namespace evoxb {
+namespace cg = cooperative_groups;
+
+constexpr int kPeelThreads = 256;
+constexpr int kPeelWarps = kPeelThreads / 32;
+constexpr int kChunkWords = 128;          // one warp-load: 32 lanes x uint4 = 512 B = 4096 columns
+constexpr int kChunkCols = kChunkWords * 32;
+constexpr int kBatch = 8;                 // rows in flight per warp (8 x 512 B)
+constexpr int kPlanesWarp = 12;           // a warp accumulates at most 2^12 - 8 rows between flushes
+constexpr int kPlanes = kPlanesWarp + 3;  // after adding the 8 warps of a CTA
+constexpr int kWarpRowsCap = (1 << kPlanesWarp) - kBatch;
+
+struct PeelCtrl {
+    int len[2];       // member count of the current / next front (double-buffered)
+    int fronts_done;  // number of fronts peeled (written at exit)
+    int pad;
+};
+
+// sum (low) and carry (high) of three bit-vectors
+__device__ __forceinline__ void csa(uint32_t &hi, uint32_t &lo, uint32_t a, uint32_t b, uint32_t c) {
+    lo = lop3_xor3(a, b, c);
+    hi = lop3_maj(a, b, c);
+}
+
+// Adds eight one-bit-per-position words into a bit-sliced counter (Harley-Seal step).
+__device__ __forceinline__ void vc_add8(uint32_t (&pl)[kPlanes], const uint32_t (&w)[kBatch]) {
+    uint32_t c0, s0, c1, s1, c2, s2, c3, d0, t0, d1, e0;
+    csa(c0, s0, w[0], w[1], w[2]);
+    csa(c1, s1, w[3], w[4], w[5]);
+    csa(c2, s2, w[6], w[7], pl[0]);
+    csa(c3, pl[0], s0, s1, s2);
+    csa(d0, t0, c0, c1, c2);
+    csa(d1, pl[1], t0, c3, pl[1]);
+    csa(e0, pl[2], d0, d1, pl[2]);
+    uint32_t carry = e0;
+#pragma unroll
+    for (int p = 3; p < kPlanesWarp; ++p) {
+        const uint32_t t = pl[p] & carry;
+        pl[p] ^= carry;
+        carry = t;
+    }
+}
+
+// Shared memory used by one CTA for the cross-warp reduction and the expansion.
+struct PeelSmem {
+    uint32_t xchg[kPeelWarps / 2][4 * kPlanes][32];  // up to 4 senders per round
+    uint32_t fin[kPlanes][kChunkWords];              // CTA totals, plane-major
+};
+
+// Streams rows members[t0..t1) (or rows t0..t1 themselves when members == nullptr), restricted to
+// the 4096-column chunk `chunk`, and adds sign * (column sums) to count[].
+__device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_words, const int *__restrict__ members,
+                                 int64_t t0, int64_t t1, int chunk, int *__restrict__ count, int sign,
+                                 PeelSmem &sm) {
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const uint4 *base = reinterpret_cast<const uint4 *>(D + (int64_t)chunk * kChunkWords) + lane;
+    const int64_t row_vec = row_words >> 2;  // row stride in uint4
+
+    for (int64_t f0 = t0; f0 < t1; f0 += (int64_t)kWarpRowsCap * kPeelWarps) {
+        const int64_t f1 = min(t1, f0 + (int64_t)kWarpRowsCap * kPeelWarps);
+        uint32_t pl[4][kPlanes];
+#pragma unroll
+        for (int s = 0; s < 4; ++s)
+#pragma unroll
+            for (int p = 0; p < kPlanes; ++p) pl[s][p] = 0u;
+
+        // warp `warp` takes rows f0 + warp, f0 + warp + 8, ... in batches of kBatch
+        for (int64_t t = f0 + warp; t < f1; t += (int64_t)kPeelWarps * kBatch) {
+            uint4 v[kBatch];
+#pragma unroll
+            for (int b = 0; b < kBatch; ++b) {
+                const int64_t tt = t + (int64_t)b * kPeelWarps;
+                if (tt < f1) {
+                    const int64_t row = members ? (int64_t)__ldcg(members + tt) : tt;  // list is rewritten every front: L2 read
+                    v[b] = ldg_stream_v4(base + row * row_vec);
+                } else {
+                    v[b] = make_uint4(0u, 0u, 0u, 0u);
+                }
+            }
+            uint32_t w[kBatch];
+#pragma unroll
+            for (int b = 0; b < kBatch; ++b) w[b] = v[b].x;
+            vc_add8(pl[0], w);
+#pragma unroll
+            for (int b = 0; b < kBatch; ++b) w[b] = v[b].y;
+            vc_add8(pl[1], w);
+#pragma unroll
+            for (int b = 0; b < kBatch; ++b) w[b] = v[b].z;
+            vc_add8(pl[2], w);
+#pragma unroll
+            for (int b = 0; b < kBatch; ++b) w[b] = v[b].w;
+            vc_add8(pl[3], w);
+        }
+
+        // ---- add the eight warps' bit-sliced counters (tree: 8 -> 4 -> 2 -> 1) ----
+#pragma unroll
+        for (int stride = 1; stride < kPeelWarps; stride <<= 1) {
+            const bool sender = (warp & (2 * stride - 1)) == stride;
+            const bool receiver = (warp & (2 * stride - 1)) == 0;
+            const int slot = warp / (2 * stride);
+            __syncthreads();
+            if (sender) {
+#pragma unroll
+                for (int s = 0; s < 4; ++s)
+#pragma unroll
+                    for (int p = 0; p < kPlanes; ++p) sm.xchg[slot][s * kPlanes + p][lane] = pl[s][p];
+            }
+            __syncthreads();
+            if (receiver) {
+#pragma unroll
+                for (int s = 0; s < 4; ++s) {
+                    uint32_t carry = 0u;
+#pragma unroll
+                    for (int p = 0; p < kPlanes; ++p) {
+                        const uint32_t b = sm.xchg[slot][s * kPlanes + p][lane];
+                        const uint32_t a = pl[s][p];
+                        pl[s][p] = lop3_xor3(a, b, carry);
+                        carry = lop3_maj(a, b, carry);
+                    }
+                }
+            }
+        }
+        if (warp == 0) {
+#pragma unroll
+            for (int s = 0; s < 4; ++s)
+#pragma unroll
+                for (int p = 0; p < kPlanes; ++p) sm.fin[p][lane * 4 + s] = pl[s][p];
+        }
+        __syncthreads();
+
+        // ---- expand: thread -> (word, 16-bit half), one atomic per non-zero column ----
+        {
+            const int wd = threadIdx.x & (kChunkWords - 1);
+            const int half = threadIdx.x >> 7;  // 256 threads = 128 words x 2 halves
+            uint32_t any = 0u;
+            uint32_t pw[kPlanes];
+#pragma unroll
+            for (int p = 0; p < kPlanes; ++p) {
+                pw[p] = sm.fin[p][wd] >> (16 * half);
+                any |= pw[p];
+            }
+            any &= 0xffffu;
+            int *cbase = count + (int64_t)chunk * kChunkCols + wd * 32 + 16 * half;
+            while (any) {
+                const int bit = __ffs(any) - 1;
+                any &= any - 1;
+                int val = 0;
+#pragma unroll
+                for (int p = 0; p < kPlanes; ++p) val |= (int)((pw[p] >> bit) & 1u) << p;
+                atomicAdd(cbase + bit, sign * val);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// Splits the (chunk, member) space evenly over the CTAs of the grid: CTA b owns the linear range
+// [b * total / G, (b + 1) * total / G) of segments ordered chunk-major, so a CTA touches at most
+// two chunks when G >= nchunks.
+__device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_words, int nchunks,
+                                 const int *__restrict__ members, int64_t nf, int *__restrict__ count, int sign,
+                                 PeelSmem &sm) {
+    const int64_t total = (int64_t)nchunks * nf;
+    const int64_t s0 = total * blockIdx.x / gridDim.x;
+    const int64_t s1 = total * (blockIdx.x + 1) / gridDim.x;
+    int64_t s = s0;
+    while (s < s1) {
+        const int chunk = (int)(s / nf);
+        const int64_t t0 = s - (int64_t)chunk * nf;
+        const int64_t t1 = min(nf, t0 + (s1 - s));
+        accumulate_chunk(D, row_words, members, t0, t1, chunk, count, sign, sm);
+        s += t1 - t0;
+    }
+}
+
+// K2: count[j] += number of rows in [0, n_rows) that dominate j   (non_dominate.py:61)
+__global__ void __launch_bounds__(kPeelThreads)
+dominator_count_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int64_t n_rows,
+                       int *__restrict__ count) {
+    __shared__ PeelSmem sm;
+    accumulate_front(D, row_words, nchunks, nullptr, n_rows, count, +1, sm);
+}
+
+// Front detection: every j < n with count[j] == 0 joins the front, gets its rank, and drops to -1
+// for good (the reference's "count -= front" trick, non_dominate.py:103).
+__device__ void collect_front(int *__restrict__ count, int n, int r, int *__restrict__ rank,
+                              const int *__restrict__ perm, int *__restrict__ list, int *__restrict__ len) {
+    const int lane = threadIdx.x & 31;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t n32 = round_up(n, 32);
+    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n32; j += stride) {
+        const bool in = (j < n) && (__ldcg(count + j) == 0);  // count is updated by L2 atomics
+        const uint32_t m = __ballot_sync(0xffffffffu, in);
+        if (m) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(len, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (in) {
+                list[base + __popc(m & ((1u << lane) - 1u))] = (int)j;
+                rank[perm ? perm[j] : j] = r;
+                count[j] = -1;
+            }
+        }
+    }
+}
+
+// K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).
+__global__ void __launch_bounds__(kPeelThreads)
+peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n,
+                       int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm,
+                       int *__restrict__ list, PeelCtrl *__restrict__ ctrl) {
+    __shared__ PeelSmem sm;
+    cg::grid_group grid = cg::this_grid();
+    int r = 0;
+    for (;;) {
+        collect_front(count, n, r, rank, perm, list, &ctrl->len[r & 1]);
+        grid.sync();
+        const int nf = *((volatile int *)&ctrl->len[r & 1]);
+        if (nf == 0) break;  // non_dominate.py:76-78: while any(front)
+        if (blockIdx.x == 0 && threadIdx.x == 0) ctrl->len[(r + 1) & 1] = 0;
+        accumulate_front(D, row_words, nchunks, list, nf, count, -1, sm);
+        grid.sync();
+        ++r;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) ctrl->fronts_done = r;
+}
+
+// ---- non-persistent pieces, used by the row-sharded multi-GPU path (host drives the loop) ----
+__global__ void __launch_bounds__(kPeelThreads)
+collect_front_kernel(int *__restrict__ count, int n, int r, int *__restrict__ rank, const int *__restrict__ perm,
+                     int *__restrict__ list, int *__restrict__ len) {
+    collect_front(count, n, r, rank, perm, list, len);
+}
+
+}  // namespace evoxb

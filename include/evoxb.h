@@ -1,0 +1,77 @@
+/*
+ * evoxb -- B200-native Pareto ranking and crowding distance (C ABI).
+ *
+ * This is the drop-in boundary for ONE hot path of EvoX (reference: MinyangChen/evox-myc,
+ * EvoX 0.8.1): multi-objective environmental selection.  The reference has no FFI layer; its
+ * boundary is two Python callables (src/evox/operators/__init__.py:1-5).  Each entry point
+ * below names the reference function it replaces (paths relative to the reference tree).
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the name says host; arrays are row-major,
+ *     dense, and never modified unless documented as outputs;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); nothing in here
+ *     calls cudaDeviceSynchronize and nothing allocates: scratch comes from the caller
+ *     (`ws`, at least *_workspace_bytes() bytes, 256-byte aligned);
+ *   - return value 0 = success, negative = error (EVOXB_E_*); evoxb_last_error() returns a
+ *     thread-local message for the last failing call on this thread;
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef EVOXB_H_
+#define EVOXB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EVOXB_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define EVOXB_API __attribute__((visibility("default")))
+#else
+#define EVOXB_API
+#endif
+
+#define EVOXB_OK 0
+#define EVOXB_E_INVALID (-1)   /* bad argument (null pointer, negative size, m out of range) */
+#define EVOXB_E_WORKSPACE (-2) /* workspace missing, misaligned or too small */
+#define EVOXB_E_CUDA (-3)      /* a CUDA runtime call failed; message has the CUDA error string */
+#define EVOXB_E_UNSUPPORTED (-4)
+#define EVOXB_E_NCCL (-5)
+
+#define EVOXB_MAX_OBJECTIVES 32
+
+typedef void *evoxb_stream_t; /* cudaStream_t */
+
+EVOXB_API int evoxb_version(void);
+EVOXB_API const char *evoxb_last_error(void);
+
+/* ---- a2: dominate_relation(x, y)  -- src/evox/utils/common.py:95-104 --------------------
+ * out[i * ny + j] = 1 iff x_i dominates y_j: all_k(x_ik <= y_jk) && any_k(x_ik < y_jk),
+ * IEEE compares (NaN => 0, -0 == +0).  x is (nx, m), y is (ny, m), out is (nx, ny) bytes.   */
+EVOXB_API int evoxb_dominate_relation_f32(const float *x, int64_t nx, const float *y, int64_t ny, int m,
+                                uint8_t *out, evoxb_stream_t stream);
+
+/* ---- a2+a3+a4: non_dominated_sort(x) -> rank ---------------------------------------------
+ * src/evox/operators/selection/non_dominate.py:30-113 (dominance matrix :60, dominator count
+ * :61, front-peeling while_loop :72-111).  fitness is (n, m) float32, rank is (n) int32,
+ * 0-based.  Bit-exact with the reference for every input, NaN / +-inf / duplicates included.
+ * The dominance matrix lives in `ws` as one bit per ordered pair (n * roundup(n,4096) / 8 bytes). */
+EVOXB_API int evoxb_nds_workspace_bytes(int64_t n, int m, size_t *bytes);
+EVOXB_API int evoxb_nds_rank_f32(const float *fitness, int64_t n, int m, int32_t *rank, void *ws,
+                       size_t ws_bytes, evoxb_stream_t stream);
+
+/* ---- profiling hook (no counterpart in the reference) --------------------------------------
+ * When enabled, every compute entry point brackets its stages with CUDA events on the caller's
+ * stream.  evoxb_profile_read() synchronises those events and returns, for the LAST call made
+ * on this thread, up to `cap` stage times in milliseconds and their names (static strings).
+ * Returns the number of stages.                                                              */
+EVOXB_API int evoxb_profile_enable(int on);
+EVOXB_API int evoxb_profile_read(float *ms, const char **names, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EVOXB_H_ */

@@ -1,0 +1,133 @@
+"""GPU parity: non_dominated_sort through the C ABI vs the oracle -- ranks must be bit-exact."""
+
+import ctypes
+
+import numpy as np
+import pytest
+
+import helpers as h
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+def _oracle_rank(x):
+    from oracle import c_oracle, nds_oracle
+
+    return nds_oracle.non_dominated_sort(x) if x.shape[0] <= 1500 else c_oracle.non_dominated_sort(x)
+
+
+def _gpu_rank(x):
+    import evox_myc_b200 as e
+
+    return e.non_dominated_sort(x)
+
+
+def test_reference_kat(kats):
+    k = kats["nds_11x2"]
+    r = _gpu_rank(np.array(k["x"], dtype=np.float32))
+    assert r.dtype == np.int32 and r.tolist() == k["rank"]
+
+
+def test_reference_monitor_kat_int32(kats):
+    k = kats["monitor_pf_int32"]
+    f1 = np.array(k["fitness1"], dtype=np.int32)  # int32 fitness is cast to float32 by the wrapper
+    pf1 = f1[_gpu_rank(f1) == 0]
+    assert pf1.tolist() == k["pf1"]
+    f2 = np.concatenate([pf1.astype(np.float32), np.array(k["fitness2"], dtype=np.float32)])
+    assert f2[_gpu_rank(f2) == 0].tolist() == k["pf2"]
+
+
+CASES = [
+    ("one", lambda: h.uniform(1, 3, 1)),
+    ("two_equal", lambda: np.ones((2, 3), np.float32)),
+    ("n31", lambda: h.uniform(31, 2, 2)),
+    ("n33", lambda: h.uniform(33, 5, 3)),
+    ("n127_m1", lambda: h.uniform(127, 1, 4)),
+    ("n129", lambda: h.nasty(129, 3, 5)),
+    ("n1000_m2", lambda: h.uniform(1000, 2, 6)),
+    ("n1025_m3", lambda: h.uniform(1025, 3, 7)),
+    ("n4097_m5", lambda: h.uniform(4097, 5, 8)),
+    ("n5000_m10", lambda: h.uniform(5000, 10, 9)),
+    ("n3000_m13_generic", lambda: h.uniform(3000, 13, 10)),
+    ("grid", lambda: h.integer_grid(6000, 3, 11, levels=8)),
+    ("grid_m2", lambda: h.integer_grid(5000, 2, 12, levels=64)),
+    ("nasty", lambda: h.nasty(7001, 4, 13)),
+    ("dtlz2", lambda: h.dtlz2(8192, 3, 12, 14)),
+    ("dtlz2_converged", lambda: h.dtlz2(8192, 3, 12, 15, converged=True)),
+    ("chain", lambda: h.chain(700, 2)),
+    ("all_nan", lambda: np.full((100, 3), np.nan, np.float32)),
+    ("all_equal", lambda: np.zeros((5000, 3), np.float32)),
+    ("uniform_16k_m3", lambda: h.uniform(16384, 3, 16)),
+    ("uniform_20k_m2_deep", lambda: h.uniform(20000, 2, 17)),
+]
+
+
+@pytest.mark.parametrize("name,gen", CASES, ids=[c[0] for c in CASES])
+def test_rank_bit_exact(name, gen):
+    x = gen()
+    want = _oracle_rank(x)
+    got = _gpu_rank(x)
+    assert got.dtype == np.int32
+    assert np.array_equal(got, want), f"{name}: {np.sum(got != want)} of {x.shape[0]} ranks differ"
+
+
+def test_device_tensor_in_device_tensor_out():
+    import evox_myc_b200 as e
+
+    x = h.uniform(3000, 3, 21)
+    r = e.non_dominated_sort(torch.from_numpy(x).cuda(), method="full map-reduce")
+    assert r.is_cuda and r.dtype == torch.int32
+    assert np.array_equal(r.cpu().numpy(), _oracle_rank(x))
+    with pytest.raises(AssertionError):
+        e.non_dominated_sort(torch.from_numpy(x).cuda(), method="bogus")
+
+
+def test_empty_population():
+    import evox_myc_b200 as e
+
+    r = e.non_dominated_sort(torch.empty((0, 3), device="cuda"))
+    assert r.shape == (0,)
+
+
+def test_repeated_calls_share_workspace():
+    """The workspace keeps the previous call's matrix; a second call must not see stale bits."""
+    a = h.uniform(5000, 3, 31)
+    b = h.integer_grid(3000, 3, 32, levels=4)
+    for x in (a, b, a, b):
+        assert np.array_equal(_gpu_rank(x), _oracle_rank(x))
+
+
+def test_dominate_relation_dense():
+    import evox_myc_b200 as e
+    from oracle import nds_oracle
+
+    x = h.nasty(300, 3, 41)
+    y = h.nasty(500, 3, 42)
+    got = e.dominate_relation(x, y)
+    assert got.dtype == bool and np.array_equal(got, nds_oracle.dominate_relation(x, y))
+
+
+def test_workspace_too_small_is_an_error():
+    from evox_myc_b200 import _lib
+
+    L = _lib.lib()
+    x = torch.rand(1000, 3, device="cuda")
+    rank = torch.empty(1000, dtype=torch.int32, device="cuda")
+    ws = torch.empty(1024, dtype=torch.uint8, device="cuda")
+    rc = L.evoxb_nds_rank_f32(x.data_ptr(), 1000, 3, rank.data_ptr(), ws.data_ptr(), ws.numel(), None)
+    assert rc == -2 and b"workspace too small" in L.evoxb_last_error()
+
+
+@pytest.mark.parametrize("n,m", [(65536, 3)])
+def test_config2_full_size_properties(n, m):
+    """BASELINE config 2 at full size: oracle comparison (C twin, a few seconds) + size-independent properties."""
+    import evox_myc_b200 as e
+
+    x = h.uniform(n, m, 51)
+    got = _gpu_rank(x)
+    assert np.array_equal(got, _oracle_rank(x))
+    # permutation invariance at full size
+    p = np.random.default_rng(5).permutation(n)
+    assert np.array_equal(_gpu_rank(x[p]), got[p])
