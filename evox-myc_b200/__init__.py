@@ -5,7 +5,22 @@ it sits behind the reference's own operator signatures.  See DESIGN.md and inclu
 """
 
 from . import _lib  # noqa: F401
-from .operators import non_dominated_sort  # noqa: F401
+from .operators import (  # noqa: F401
+    NonDominate,
+    crowding_distance,
+    crowding_distance_sort,
+    non_dominate,
+    non_dominated_sort,
+    nsga2_select,
+)
 from .utils import dominate_relation  # noqa: F401
 
-__all__ = ["non_dominated_sort", "dominate_relation"]
+__all__ = [
+    "non_dominated_sort",
+    "crowding_distance",
+    "crowding_distance_sort",
+    "non_dominate",
+    "NonDominate",
+    "nsga2_select",
+    "dominate_relation",
+]

@@ -21,6 +21,14 @@ EXPORTS = [
     "evoxb_dominate_relation_f32",
     "evoxb_nds_workspace_bytes",
     "evoxb_nds_rank_f32",
+    "evoxb_crowding_workspace_bytes",
+    "evoxb_crowding_f32",
+    "evoxb_nsga2_select_workspace_bytes",
+    "evoxb_nsga2_select_f32",
+    "evoxb_non_dominate_select_f32",
+    "evoxb_argsort_workspace_bytes",
+    "evoxb_argsort_f32",
+    "evoxb_gather_rows_f32",
     "evoxb_profile_enable",
     "evoxb_profile_read",
 ]
@@ -47,6 +55,14 @@ def lib() -> ctypes.CDLL:
         L.evoxb_dominate_relation_f32.argtypes = [vp, i64, vp, i64, i32, vp, vp]
         L.evoxb_nds_workspace_bytes.argtypes = [i64, i32, ctypes.POINTER(sz)]
         L.evoxb_nds_rank_f32.argtypes = [vp, i64, i32, vp, vp, sz, vp]
+        L.evoxb_crowding_workspace_bytes.argtypes = [i64, i32, ctypes.POINTER(sz)]
+        L.evoxb_crowding_f32.argtypes = [vp, vp, i64, i32, vp, vp, sz, vp]
+        L.evoxb_nsga2_select_workspace_bytes.argtypes = [i64, i32, ctypes.POINTER(sz)]
+        L.evoxb_nsga2_select_f32.argtypes = [vp, i64, i32, i64, vp, vp, vp, vp, sz, vp]
+        L.evoxb_non_dominate_select_f32.argtypes = [vp, i64, i32, i64, vp, vp, sz, vp]
+        L.evoxb_argsort_workspace_bytes.argtypes = [i64, ctypes.POINTER(sz)]
+        L.evoxb_argsort_f32.argtypes = [vp, i64, vp, vp, sz, vp]
+        L.evoxb_gather_rows_f32.argtypes = [vp, i64, i64, vp, i64, vp, vp]
         L.evoxb_profile_enable.argtypes = [i32]
         L.evoxb_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]
         for name in EXPORTS:

@@ -3,6 +3,9 @@
 #include "common.cuh"
 #include "dominance.cuh"
 #include "peel.cuh"
+#include "sort.cuh"
+#include "crowding.cuh"
+#include "select.cuh"
 
 namespace evoxb {
 
@@ -60,6 +63,110 @@ static int peel_grid(int *blocks) {
     }
     *blocks = cached_blocks;
     return 0;
+}
+
+}  // namespace evoxb
+
+
+namespace evoxb {
+
+// Enqueues the whole ranking (K0..K3) on `s`.  `L` must come from nds_layout(ws, n, m, n).
+static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const NdsLayout &L, cudaStream_t s,
+                   Profiler &prof) {
+    prof.mark("prep", s);
+    EVOXB_CUDA(cudaMemsetAsync(L.ctrl, 0, sizeof(PeelCtrl), s));
+    EVOXB_CUDA(cudaMemsetAsync(L.count, 0, sizeof(int) * (size_t)L.npad, s));
+    transpose_pad_kernel<<<(unsigned)div_up(L.npad, 256), 256, 0, s>>>(fitness, n, m, L.npad, L.xt);
+    EVOXB_LAUNCH_CHECK("transpose_pad_kernel");
+
+    prof.mark("dominance_build", s);
+    if (int rc = launch_dominance_build(L.xt, L.npad, 0, n, m, L.D, L.row_words, s)) return rc;
+
+    int blocks = 0;
+    if (int rc = peel_grid(&blocks)) return rc;
+
+    prof.mark("dominator_count", s);
+    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, L.count);
+    EVOXB_LAUNCH_CHECK("dominator_count_kernel");
+
+    prof.mark("peel", s);
+    {
+        const uint32_t *D = L.D;
+        int64_t row_words = L.row_words;
+        int nchunks = L.nchunks;
+        int nn = (int)n;
+        int *count = L.count;
+        int *rk = rank;
+        const int *perm = nullptr;
+        int *list = L.list;
+        PeelCtrl *ctrl = L.ctrl;
+        void *args[] = {&D, &row_words, &nchunks, &nn, &count, &rk, &perm, &list, &ctrl};
+        EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_persistent_kernel, dim3(blocks), dim3(kPeelThreads),
+                                               args, 0, s));
+    }
+    return 0;
+}
+
+struct SelectLayout {
+    NdsLayout nds;
+    CrowdLayout crowd;
+    SortBufs sb;
+    int *hist;
+    int *worst;
+    uint8_t *mask;
+    int *rank;
+    float *crowd_out;
+    size_t bytes;
+};
+
+struct ArgsortLayout {
+    SortBufs sb;
+    size_t bytes;
+};
+
+static ArgsortLayout argsort_layout(void *ws, int64_t n) {
+    ArgsortLayout A{};
+    Carver c(ws);
+    const int64_t n1 = n > 0 ? n : 1;
+    A.sb.cap = round_up(n1, 4);
+    A.sb.tiles = (int)div_up(A.sb.cap, kSortTile);
+    for (int b = 0; b < 2; ++b) {
+        A.sb.keys[b] = c.take<uint32_t>((size_t)A.sb.cap);
+        A.sb.vals[b] = c.take<uint32_t>((size_t)A.sb.cap);
+    }
+    A.sb.hist = c.take<uint32_t>(sort_hist_words(A.sb.cap, 1));
+    A.bytes = c.total();
+    return A;
+}
+
+static SelectLayout select_layout(void *ws, int64_t n, int m) {
+    SelectLayout S{};
+    Carver c(ws);
+    const int64_t n1 = n > 0 ? n : 1;
+    S.worst = c.take<int>(64);
+    S.hist = c.take<int>((size_t)n1);
+    S.mask = c.take<uint8_t>((size_t)n1);
+    S.rank = c.take<int>((size_t)n1);
+    S.crowd_out = c.take<float>((size_t)n1);
+    S.sb.cap = round_up(n1, 4);
+    S.sb.tiles = (int)div_up(S.sb.cap, kSortTile);
+    for (int b = 0; b < 2; ++b) {
+        S.sb.keys[b] = c.take<uint32_t>((size_t)S.sb.cap);
+        S.sb.vals[b] = c.take<uint32_t>((size_t)S.sb.cap);
+    }
+    S.sb.hist = c.take<uint32_t>(sort_hist_words(S.sb.cap, 1));
+    {
+        char *sub = c.take<char>(0);
+        S.crowd = crowd_layout(sub, n, m);
+        c.take<char>(S.crowd.bytes);
+    }
+    {
+        char *sub = c.take<char>(0);
+        S.nds = nds_layout(sub, n, m, n);
+        c.take<char>(S.nds.bytes);
+    }
+    S.bytes = c.total();
+    return S;
 }
 
 }  // namespace evoxb
@@ -127,39 +234,149 @@ EVOXB_API int evoxb_nds_rank_f32(const float *fitness, int64_t n, int m, int32_t
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     Profiler &prof = profiler();
     prof.begin();
+    if (int rc = run_nds(fitness, n, m, rank, L, s, prof)) return rc;
+    prof.mark("end", s);
+    return 0;
+}
 
-    prof.mark("prep", s);
-    EVOXB_CUDA(cudaMemsetAsync(L.ctrl, 0, sizeof(PeelCtrl), s));
-    EVOXB_CUDA(cudaMemsetAsync(L.count, 0, sizeof(int) * (size_t)L.npad, s));
-    transpose_pad_kernel<<<(unsigned)div_up(L.npad, 256), 256, 0, s>>>(fitness, n, m, L.npad, L.xt);
-    EVOXB_LAUNCH_CHECK("transpose_pad_kernel");
+EVOXB_API int evoxb_crowding_workspace_bytes(int64_t n, int m, size_t *bytes) {
+    if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
+    if (int rc = check_common((const void *)1, n, m)) return rc;
+    *bytes = crowd_layout(nullptr, n, m).bytes;
+    return 0;
+}
 
-    prof.mark("dominance_build", s);
-    if (int rc = launch_dominance_build(L.xt, L.npad, 0, n, m, L.D, L.row_words, s)) return rc;
+EVOXB_API int evoxb_crowding_f32(const float *fitness, const uint8_t *mask, int64_t n, int m, float *dist, void *ws,
+                       size_t ws_bytes, evoxb_stream_t stream) {
+    if (int rc = check_common(fitness, n, m)) return rc;
+    if (n == 0) return 0;
+    if (!dist) return fail(EVOXB_E_INVALID, "dist is null");
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
+    CrowdLayout L = crowd_layout(ws, n, m);
+    if (ws_bytes < L.bytes)
+        return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, L.bytes);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Profiler &prof = profiler();
+    prof.begin();
+    prof.mark("crowding", s);
+    if (int rc = launch_crowding(fitness, mask, n, m, dist, L, s)) return rc;
+    prof.mark("end", s);
+    return 0;
+}
 
-    int blocks = 0;
-    if (int rc = peel_grid(&blocks)) return rc;
+EVOXB_API int evoxb_nsga2_select_workspace_bytes(int64_t n, int m, size_t *bytes) {
+    if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
+    if (int rc = check_common((const void *)1, n, m)) return rc;
+    *bytes = select_layout(nullptr, n, m).bytes;
+    return 0;
+}
 
-    prof.mark("dominator_count", s);
-    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, L.count);
-    EVOXB_LAUNCH_CHECK("dominator_count_kernel");
+// variant 0: NSGA2.tell (nsga2.py:90-96): k-th rank at index pop_size, secondary key -crowding distance.
+// variant 1: operator non_dominate (non_dominate.py:181-195): k-th rank at index topk-1, and the
+//            secondary key is -argsort(crowding distance) taken positionally (the reference's quirk, :192-194).
+static int select_impl(int variant, const float *fitness, int64_t n, int m, int64_t pop_size, int32_t *order,
+                       int32_t *rank_out, float *crowd_out, void *ws, size_t ws_bytes, evoxb_stream_t stream) {
+    if (int rc = check_common(fitness, n, m)) return rc;
+    const int64_t kth = variant == 0 ? pop_size : pop_size - 1;
+    // rank[order[kth]] must exist (nsga2.py:92 / non_dominate.py:190)
+    if (kth < 0 || kth >= n || pop_size > n)
+        return fail(EVOXB_E_INVALID, "%s out of range (got %lld, n = %lld)", variant == 0 ? "pop_size" : "topk",
+                    (long long)pop_size, (long long)n);
+    if (!order && pop_size > 0) return fail(EVOXB_E_INVALID, "order is null");
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
+    SelectLayout S = select_layout(ws, n, m);
+    if (ws_bytes < S.bytes)
+        return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, S.bytes);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Profiler &prof = profiler();
+    prof.begin();
+    int *rank = rank_out ? rank_out : S.rank;
+    float *crowd = crowd_out ? crowd_out : S.crowd_out;
+    if (int rc = run_nds(fitness, n, m, rank, S.nds, s, prof)) return rc;
 
-    prof.mark("peel", s);
-    {
-        const uint32_t *D = L.D;
-        int64_t row_words = L.row_words;
-        int nchunks = L.nchunks;
-        int nn = (int)n;
-        int *count = L.count;
-        int *rk = rank;
-        const int *perm = nullptr;
-        int *list = L.list;
-        PeelCtrl *ctrl = L.ctrl;
-        void *args[] = {&D, &row_words, &nchunks, &nn, &count, &rk, &perm, &list, &ctrl};
-        EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_persistent_kernel, dim3(blocks), dim3(kPeelThreads),
-                                               args, 0, s));
+    prof.mark("worst_rank", s);
+    const unsigned gb = (unsigned)div_up(n, 256);
+    EVOXB_CUDA(cudaMemsetAsync(S.hist, 0, sizeof(int) * (size_t)n, s));
+    rank_hist_kernel<<<gb, 256, 0, s>>>(rank, n, S.hist);
+    EVOXB_LAUNCH_CHECK("rank_hist_kernel");
+    kth_rank_kernel<<<1, 1024, 0, s>>>(S.hist, n, kth, S.worst);
+    EVOXB_LAUNCH_CHECK("kth_rank_kernel");
+    rank_mask_kernel<<<gb, 256, 0, s>>>(rank, n, S.worst, S.mask);
+    EVOXB_LAUNCH_CHECK("rank_mask_kernel");
+
+    prof.mark("crowding", s);
+    if (int rc = launch_crowding(fitness, S.mask, n, m, crowd, S.crowd, s)) return rc;
+
+    prof.mark("select_sort", s);
+    int cur = 0;
+    if (variant == 0) {
+        neg_crowd_keys_kernel<<<gb, 256, 0, s>>>(crowd, n, S.sb.keys[0], S.sb.vals[0]);
+        EVOXB_LAUNCH_CHECK("neg_crowd_keys_kernel");
+        if (int rc = radix_sort_pairs(S.sb, 0, 1, n, nullptr, 0, 32, s, &cur)) return rc;
+    } else {
+        crowd_keys_kernel<<<gb, 256, 0, s>>>(crowd, n, S.sb.keys[0], S.sb.vals[0]);
+        EVOXB_LAUNCH_CHECK("crowd_keys_kernel");
+        if (int rc = radix_sort_pairs(S.sb, 0, 1, n, nullptr, 0, 32, s, &cur)) return rc;  // vals = argsort(crowd)
+        neg_index_keys_kernel<<<gb, 256, 0, s>>>(S.sb.vals[cur], n, S.sb.keys[cur ^ 1], S.sb.vals[cur ^ 1]);
+        EVOXB_LAUNCH_CHECK("neg_index_keys_kernel");
+        cur ^= 1;
+        if (int rc = radix_sort_pairs(S.sb, cur, 1, n, nullptr, 0, round_up(bits_for(n), 8), s, &cur)) return rc;
+    }
+    gather_rank_keys_kernel<<<gb, 256, 0, s>>>(rank, S.sb.vals[cur], n, S.sb.keys[cur]);
+    EVOXB_LAUNCH_CHECK("gather_rank_keys_kernel");
+    if (int rc = radix_sort_pairs(S.sb, cur, 1, n, nullptr, 0, round_up(bits_for(n), 8), s, &cur)) return rc;
+    if (pop_size > 0) {
+        take_prefix_kernel<<<(unsigned)div_up(pop_size, 256), 256, 0, s>>>(S.sb.vals[cur], pop_size, order);
+        EVOXB_LAUNCH_CHECK("take_prefix_kernel");
     }
     prof.mark("end", s);
+    return 0;
+}
+
+EVOXB_API int evoxb_nsga2_select_f32(const float *fitness, int64_t n, int m, int64_t pop_size, int32_t *order, int32_t *rank_out,
+                           float *crowd_out, void *ws, size_t ws_bytes, evoxb_stream_t stream) {
+    return select_impl(0, fitness, n, m, pop_size, order, rank_out, crowd_out, ws, ws_bytes, stream);
+}
+
+EVOXB_API int evoxb_non_dominate_select_f32(const float *fitness, int64_t n, int m, int64_t topk, int32_t *order, void *ws,
+                                  size_t ws_bytes, evoxb_stream_t stream) {
+    return select_impl(1, fitness, n, m, topk, order, nullptr, nullptr, ws, ws_bytes, stream);
+}
+
+EVOXB_API int evoxb_argsort_workspace_bytes(int64_t n, size_t *bytes) {
+    if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
+    if (n < 0) return fail(EVOXB_E_INVALID, "n must be >= 0");
+    *bytes = argsort_layout(nullptr, n).bytes;
+    return 0;
+}
+
+EVOXB_API int evoxb_argsort_f32(const float *x, int64_t n, int32_t *idx, void *ws, size_t ws_bytes, evoxb_stream_t stream) {
+    if (n < 0) return fail(EVOXB_E_INVALID, "n must be >= 0");
+    if (n == 0) return 0;
+    if (!x || !idx) return fail(EVOXB_E_INVALID, "null pointer");
+    if (n > (int64_t)1 << 24) return fail(EVOXB_E_UNSUPPORTED, "n exceeds 2^24");
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
+    ArgsortLayout A = argsort_layout(ws, n);
+    if (ws_bytes < A.bytes) return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, A.bytes);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const unsigned gb = (unsigned)div_up(n, 256);
+    crowd_keys_kernel<<<gb, 256, 0, s>>>(x, n, A.sb.keys[0], A.sb.vals[0]);
+    EVOXB_LAUNCH_CHECK("crowd_keys_kernel");
+    int cur = 0;
+    if (int rc = radix_sort_pairs(A.sb, 0, 1, n, nullptr, 0, 32, s, &cur)) return rc;
+    take_prefix_kernel<<<gb, 256, 0, s>>>(A.sb.vals[cur], n, idx);
+    EVOXB_LAUNCH_CHECK("take_prefix_kernel");
+    return 0;
+}
+
+EVOXB_API int evoxb_gather_rows_f32(const float *src, int64_t n, int64_t d, const int32_t *idx, int64_t k, float *dst,
+                          evoxb_stream_t stream) {
+    if (n < 0 || d < 0 || k < 0) return fail(EVOXB_E_INVALID, "negative size");
+    if (k == 0 || d == 0) return 0;
+    if (!src || !idx || !dst) return fail(EVOXB_E_INVALID, "null pointer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    gather_rows_kernel<<<(unsigned)div_up(k * d, 256), 256, 0, s>>>(src, d, idx, k, dst);
+    EVOXB_LAUNCH_CHECK("gather_rows_kernel");
     return 0;
 }
 

@@ -51,3 +51,125 @@ def non_dominated_sort(x, method: str = "auto"):
                                      rt.stream_ptr(a.dev.device))
             )
     return rt.give_back(rank, a, "nds_rank")
+
+
+def _ws_call(size_fn, size_args, device):
+    need = ctypes.c_size_t()
+    _lib.check(size_fn(*size_args, ctypes.byref(need)))
+    return rt.workspace(need.value, device)
+
+
+def crowding_distance(costs, mask=None):
+    """Crowding distance -- non_dominate.py:116-156.
+
+    ``costs`` is (n, m); ``mask`` is None or a boolean (n,) array, True = the row takes part.
+    Returns float32 (n,): ignored rows are ``-inf``, the two ends of every objective ``+inf``.
+    """
+    L = _lib.lib()
+    a = rt.Arg(costs, torch.float32, "cd_x")
+    _check_2d(a, "costs")
+    n, m = a.dev.shape
+    mk = None
+    if mask is not None:
+        mk = rt.Arg(mask, torch.uint8, "cd_mask", device=a.dev.device)
+        if tuple(mk.dev.shape) != (n,):
+            raise ValueError(f"mask must have shape ({n},), got {tuple(mk.dev.shape)}")
+    dist = torch.empty((n,), dtype=torch.float32, device=a.dev.device)
+    if n > 0:
+        with torch.cuda.device(a.dev.device):
+            ws = _ws_call(L.evoxb_crowding_workspace_bytes, (n, m), a.dev.device)
+            _lib.check(
+                L.evoxb_crowding_f32(a.dev.data_ptr(), mk.dev.data_ptr() if mk is not None else None, n, m,
+                                     dist.data_ptr(), ws.data_ptr(), ws.numel(), rt.stream_ptr(a.dev.device))
+            )
+    return rt.give_back(dist, a, "cd_out")
+
+
+def _argsort_f32(x_dev: torch.Tensor) -> torch.Tensor:
+    L = _lib.lib()
+    n = x_dev.shape[0]
+    idx = torch.empty((n,), dtype=torch.int32, device=x_dev.device)
+    if n > 0:
+        with torch.cuda.device(x_dev.device):
+            ws = _ws_call(L.evoxb_argsort_workspace_bytes, (n,), x_dev.device)
+            _lib.check(L.evoxb_argsort_f32(x_dev.data_ptr(), n, idx.data_ptr(), ws.data_ptr(), ws.numel(),
+                                           rt.stream_ptr(x_dev.device)))
+    return idx
+
+
+def crowding_distance_sort(x, mask=None):
+    """Indices that sort ``x`` by crowding distance -- non_dominate.py:159-178 (``jnp.argsort(distance)``)."""
+    a = rt.Arg(x, torch.float32, "cd_x")
+    mk = None if mask is None else rt.Arg(mask, torch.uint8, "cd_mask", device=a.dev.device).dev
+    dist = crowding_distance(a.dev, mk)
+    return rt.give_back(_argsort_f32(dist), a, "cds_out")
+
+
+def _gather_rows(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    L = _lib.lib()
+    flat = src.reshape(src.shape[0], -1)
+    if flat.dtype != torch.float32:
+        return src[idx.long()]  # non-float payloads (never on the hot path) use plain indexing
+    flat = flat.contiguous()
+    out = torch.empty((idx.shape[0], flat.shape[1]), dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        _lib.check(L.evoxb_gather_rows_f32(flat.data_ptr(), flat.shape[0], flat.shape[1], idx.data_ptr(), idx.shape[0],
+                                           out.data_ptr(), rt.stream_ptr(src.device)))
+    return out.reshape((idx.shape[0],) + tuple(src.shape[1:]))
+
+
+def non_dominate(population, fitness, topk: int):
+    """Select the ``topk`` individuals by Pareto rank with crowding as tie-breaker -- non_dominate.py:181-195.
+
+    Returns ``(population[order], fitness[order])``.  Follows the reference to the letter, including the
+    cut at ``rank[order[topk-1]]`` and the use of the argsort *indices* as secondary key (:190-194).
+    """
+    L = _lib.lib()
+    f = rt.Arg(fitness, torch.float32, "sel_f")
+    p = rt.Arg(population, torch.float32, "sel_p", device=f.dev.device)
+    _check_2d(f, "fitness")
+    n, m = f.dev.shape
+    order = torch.empty((topk,), dtype=torch.int32, device=f.dev.device)
+    with torch.cuda.device(f.dev.device):
+        ws = _ws_call(L.evoxb_nsga2_select_workspace_bytes, (n, m), f.dev.device)
+        _lib.check(L.evoxb_non_dominate_select_f32(f.dev.data_ptr(), n, m, topk, order.data_ptr(), ws.data_ptr(),
+                                                   ws.numel(), rt.stream_ptr(f.dev.device)))
+    return (rt.give_back(_gather_rows(p.dev, order), p, "sel_po"), rt.give_back(_gather_rows(f.dev, order), f, "sel_fo"))
+
+
+class NonDominate:
+    """Operator form of :func:`non_dominate` -- non_dominate.py:198-204."""
+
+    def __init__(self, topk):
+        self.topk = topk
+
+    def __call__(self, population, fitness):
+        return non_dominate(population, fitness, self.topk)
+
+
+def nsga2_select(merged_fitness, pop_size: int, return_details: bool = False):
+    """Survivor indices of ``NSGA2.tell`` -- src/evox/algorithms/mo/nsga2.py:90-96.
+
+    ``combined_order = lexsort((-crowding_dis, rank))[:pop_size]`` with
+    ``worst_rank = rank[argsort(rank)[pop_size]]`` (index ``pop_size``, as the reference has it).
+    Returns int32 (pop_size,); with ``return_details`` also ``rank`` and ``crowding_dis``.
+    """
+    L = _lib.lib()
+    f = rt.Arg(merged_fitness, torch.float32, "sel_f")
+    _check_2d(f, "merged_fitness")
+    n, m = f.dev.shape
+    dev = f.dev.device
+    order = torch.empty((pop_size,), dtype=torch.int32, device=dev)
+    rank = torch.empty((n,), dtype=torch.int32, device=dev) if return_details else None
+    crowd = torch.empty((n,), dtype=torch.float32, device=dev) if return_details else None
+    with torch.cuda.device(dev):
+        ws = _ws_call(L.evoxb_nsga2_select_workspace_bytes, (n, m), dev)
+        _lib.check(
+            L.evoxb_nsga2_select_f32(f.dev.data_ptr(), n, m, pop_size, order.data_ptr(),
+                                     rank.data_ptr() if rank is not None else None,
+                                     crowd.data_ptr() if crowd is not None else None,
+                                     ws.data_ptr(), ws.numel(), rt.stream_ptr(dev))
+        )
+    if return_details:
+        return (rt.give_back(order, f, "sel_o"), rt.give_back(rank, f, "sel_r"), rt.give_back(crowd, f, "sel_c"))
+    return rt.give_back(order, f, "sel_o")

@@ -63,6 +63,44 @@ EVOXB_API int evoxb_nds_workspace_bytes(int64_t n, int m, size_t *bytes);
 EVOXB_API int evoxb_nds_rank_f32(const float *fitness, int64_t n, int m, int32_t *rank, void *ws,
                        size_t ws_bytes, evoxb_stream_t stream);
 
+/* ---- a5: crowding_distance(costs, mask) -> dist ---------------------------------------------
+ * src/evox/operators/selection/non_dominate.py:116-156.  fitness is (n, m) float32; mask is (n)
+ * bytes (non-zero = participates) or NULL for "all rows"; dist is (n) float32: +inf at both ends
+ * of every objective's sorted order, -inf for masked-out rows, NaN where the reference gives NaN
+ * (range == 0).  Stable per-objective sort (NaN last, -0 == +0) as jnp.lexsort((cost, ~mask)).   */
+EVOXB_API int evoxb_crowding_workspace_bytes(int64_t n, int m, size_t *bytes);
+EVOXB_API int evoxb_crowding_f32(const float *fitness, const uint8_t *mask, int64_t n, int m, float *dist,
+                                 void *ws, size_t ws_bytes, evoxb_stream_t stream);
+
+/* ---- a7: NSGA-II survivor selection ------------------------------------------------------------
+ * src/evox/algorithms/mo/nsga2.py:90-96 (same block: gde3.py:88-97, im_moea.py:131-141):
+ * rank = non_dominated_sort(fitness); worst_rank = rank[argsort(rank)[pop_size]];
+ * crowd = crowding_distance(fitness, rank == worst_rank);
+ * order = lexsort((-crowd, rank))[:pop_size].  Requires 0 <= pop_size < n like the reference's
+ * indexing.  order is (pop_size) int32; rank_out (n) and crowd_out (n) are optional (may be NULL). */
+EVOXB_API int evoxb_nsga2_select_workspace_bytes(int64_t n, int m, size_t *bytes);
+EVOXB_API int evoxb_nsga2_select_f32(const float *fitness, int64_t n, int m, int64_t pop_size, int32_t *order,
+                                     int32_t *rank_out, float *crowd_out, void *ws, size_t ws_bytes,
+                                     evoxb_stream_t stream);
+
+/* ---- a6: operator form non_dominate(population, fitness, topk) ------------------------------------
+ * src/evox/operators/selection/non_dominate.py:181-195, including its quirks: the cut-off rank is
+ * rank[argsort(rank)[topk-1]] (:190) and the secondary sort key is -argsort(crowding distance)
+ * used positionally (:191-194).  Requires 1 <= topk <= n.  order is (topk) int32.  Workspace size
+ * is evoxb_nsga2_select_workspace_bytes().                                                         */
+EVOXB_API int evoxb_non_dominate_select_f32(const float *fitness, int64_t n, int m, int64_t topk, int32_t *order,
+                                            void *ws, size_t ws_bytes, evoxb_stream_t stream);
+
+/* ---- a6: crowding_distance_sort = jnp.argsort(distance)  (non_dominate.py:159-178) -------------------
+ * Stable ascending argsort of n floats with lax.sort ordering (NaN last, -0 == +0).                  */
+EVOXB_API int evoxb_argsort_workspace_bytes(int64_t n, size_t *bytes);
+EVOXB_API int evoxb_argsort_f32(const float *x, int64_t n, int32_t *idx, void *ws, size_t ws_bytes,
+                                evoxb_stream_t stream);
+
+/* survivor = merged_pop[order]  (nsga2.py:97-98): dst[r, :] = src[idx[r], :], src is (n, d), dst (k, d). */
+EVOXB_API int evoxb_gather_rows_f32(const float *src, int64_t n, int64_t d, const int32_t *idx, int64_t k,
+                                    float *dst, evoxb_stream_t stream);
+
 /* ---- profiling hook (no counterpart in the reference) --------------------------------------
  * When enabled, every compute entry point brackets its stages with CUDA events on the caller's
  * stream.  evoxb_profile_read() synchronises those events and returns, for the LAST call made

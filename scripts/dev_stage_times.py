@@ -24,3 +24,13 @@ for n, m in cfgs:
                       "stages_ms": {k: round(v, 3) for k, v in st.items()},
                       "pairs_per_s": n * n / (tot * 1e-3), "peel_GBs": round(peel_gbs, 1), "count_GBs": round(cnt_gbs, 1),
                       "build_pairs_per_s": n * n / (st["dominance_build"] * 1e-3)}))
+
+print("--- nsga2_select (NDS + crowding + selection sort) ---")
+for n, m in cfgs:
+    x = torch.from_numpy(np.random.default_rng(0).random((n, m), dtype=np.float32)).cuda()
+    for it in range(3):
+        torch.cuda.synchronize()
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        t0.record(); o = e.nsga2_select(x, n // 2); t1.record(); torch.cuda.synchronize()
+        st = _lib.profile_read()
+    print(json.dumps({"n": n, "m": m, "total_ms": round(t0.elapsed_time(t1), 3), "stages_ms": {k: round(v, 3) for k, v in st.items()}}))
