@@ -31,6 +31,7 @@ EXPORTS = [
     "evoxb_gather_rows_f32",
     "evoxb_profile_enable",
     "evoxb_profile_read",
+    "evoxb_launch_count",
 ]
 
 
@@ -63,6 +64,7 @@ def lib() -> ctypes.CDLL:
         L.evoxb_argsort_workspace_bytes.argtypes = [i64, ctypes.POINTER(sz)]
         L.evoxb_argsort_f32.argtypes = [vp, i64, vp, vp, sz, vp]
         L.evoxb_gather_rows_f32.argtypes = [vp, i64, i64, vp, i64, vp, vp]
+        L.evoxb_launch_count.restype = ctypes.c_ulonglong
         L.evoxb_profile_enable.argtypes = [i32]
         L.evoxb_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]
         for name in EXPORTS:
@@ -74,6 +76,10 @@ def lib() -> ctypes.CDLL:
 def check(rc: int) -> None:
     if rc != 0:
         raise EvoxbError(rc, lib().evoxb_last_error().decode("utf-8", "replace"))
+
+
+def launch_count() -> int:
+    return int(lib().evoxb_launch_count())
 
 
 def profile_enable(on: bool) -> None:

@@ -33,6 +33,7 @@ inline int fail(int code, const char *fmt, ...) {
 
 #define EVOXB_LAUNCH_CHECK(name)                                                                 \
     do {                                                                                         \
+        ++::evoxb::g_launches;                                                                   \
         cudaError_t e__ = cudaGetLastError();                                                    \
         if (e__ != cudaSuccess)                                                                  \
             return ::evoxb::fail(EVOXB_E_CUDA, "launch of %s failed at %s:%d: %s", name,         \
@@ -105,6 +106,7 @@ inline Profiler &profiler() {
     return p;
 }
 extern bool g_profile_enabled;
+extern unsigned long long g_launches;  // kernels launched by this library since load (not thread-safe: a statistic)
 
 // ---- small device helpers ---------------------------------------------------------------------
 __device__ __forceinline__ uint32_t lop3_xor3(uint32_t a, uint32_t b, uint32_t c) {

@@ -10,6 +10,7 @@
 namespace evoxb {
 
 bool g_profile_enabled = false;
+unsigned long long g_launches = 0;
 
 struct NdsLayout {
     int64_t n, npad, row_words;
@@ -103,6 +104,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         void *args[] = {&D, &row_words, &nchunks, &nn, &count, &rk, &perm, &list, &ctrl};
         EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_persistent_kernel, dim3(blocks), dim3(kPeelThreads),
                                                args, 0, s));
+        ++g_launches;
     }
     return 0;
 }
@@ -183,6 +185,8 @@ EVOXB_API int evoxb_profile_enable(int on) {
     profiler().enabled = on != 0;
     return 0;
 }
+
+EVOXB_API unsigned long long evoxb_launch_count(void) { return g_launches; }
 
 EVOXB_API int evoxb_profile_read(float *ms, const char **names, int cap) {
     Profiler &p = profiler();

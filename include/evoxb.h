@@ -108,6 +108,8 @@ EVOXB_API int evoxb_gather_rows_f32(const float *src, int64_t n, int64_t d, cons
  * Returns the number of stages.                                                              */
 EVOXB_API int evoxb_profile_enable(int on);
 EVOXB_API int evoxb_profile_read(float *ms, const char **names, int cap);
+/* Number of kernels this library has launched since it was loaded (a statistic for bench.py). */
+EVOXB_API unsigned long long evoxb_launch_count(void);
 
 #ifdef __cplusplus
 }
