@@ -23,6 +23,7 @@ EXPORTS = [
     "evoxb_nds_rank_f32",
     "evoxb_crowding_workspace_bytes",
     "evoxb_crowding_f32",
+    "evoxb_crowding_noalloc_f32",
     "evoxb_nsga2_select_workspace_bytes",
     "evoxb_nsga2_select_f32",
     "evoxb_non_dominate_select_f32",
@@ -58,6 +59,7 @@ def lib() -> ctypes.CDLL:
         L.evoxb_nds_rank_f32.argtypes = [vp, i64, i32, vp, vp, sz, vp]
         L.evoxb_crowding_workspace_bytes.argtypes = [i64, i32, ctypes.POINTER(sz)]
         L.evoxb_crowding_f32.argtypes = [vp, vp, i64, i32, vp, vp, sz, vp]
+        L.evoxb_crowding_noalloc_f32.argtypes = [vp, vp, i64, i32, vp, vp]
         L.evoxb_nsga2_select_workspace_bytes.argtypes = [i64, i32, ctypes.POINTER(sz)]
         L.evoxb_nsga2_select_f32.argtypes = [vp, i64, i32, i64, vp, vp, vp, vp, sz, vp]
         L.evoxb_non_dominate_select_f32.argtypes = [vp, i64, i32, i64, vp, vp, sz, vp]

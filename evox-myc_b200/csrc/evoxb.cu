@@ -1,5 +1,7 @@
 // C-ABI entry points of libevoxb.so (see include/evoxb.h).  Hand-written sm_100a CUDA only:
 // no CPU fallback, no library kernels on the compute path.
+#include <mutex>
+
 #include "common.cuh"
 #include "dominance.cuh"
 #include "peel.cuh"
@@ -382,6 +384,70 @@ EVOXB_API int evoxb_gather_rows_f32(const float *src, int64_t n, int64_t d, cons
     gather_rows_kernel<<<(unsigned)div_up(k * d, 256), 256, 0, s>>>(src, d, idx, k, dst);
     EVOXB_LAUNCH_CHECK("gather_rows_kernel");
     return 0;
+}
+
+}  // extern "C"
+
+// ---- crowding distance for callers that cannot allocate device memory -------------------------
+// Scratch for evoxb_crowding_noalloc_f32: part of the library image, so every GPU that loads
+// libevoxb.so holds these 8 MiB until the process exits.  In host code the name below is only a
+// host-side handle of the symbol, not a device address; the address is looked up once per
+// device with cudaGetSymbolAddress (noalloc_scratch_for_current_device) and that pointer is what
+// the kernels receive.
+#define EVOXB_NOALLOC_SCRATCH_BYTES EVOXB_CROWDING_NOALLOC_MAX_BYTES
+static __device__ __align__(256) unsigned char g_noalloc_scratch[EVOXB_NOALLOC_SCRATCH_BYTES];
+
+namespace evoxb {
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static void *g_noalloc_ptr[kMaxDevices] = {};
+
+// Device address of g_noalloc_scratch on the CURRENT device.  The first call on a device asks the
+// runtime for the symbol's address (which may load the module on that device); later calls only
+// read the cached pointer.
+static int noalloc_scratch_for_current_device(void **out) {
+    int dev = -1;
+    EVOXB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(EVOXB_E_UNSUPPORTED, "device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fail(EVOXB_E_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) failed on device %d: %s", dev,
+                        cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = ptr;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+
+}  // namespace evoxb
+
+extern "C" {
+
+// Same result as evoxb_crowding_f32, with the sort buffers taken from the library's own static
+// device array instead of a caller workspace.  See include/evoxb.h for the contract.
+EVOXB_API int evoxb_crowding_noalloc_f32(const float *fitness, const uint8_t *mask, int64_t n, int m, float *dist,
+                                         evoxb_stream_t stream) {
+    if (int rc = check_common(fitness, n, m)) return rc;
+    if (n == 0) return 0;
+    if (!dist) return fail(EVOXB_E_INVALID, "dist is null");
+    const size_t need = crowd_layout(nullptr, n, m).bytes;
+    if (need > EVOXB_NOALLOC_SCRATCH_BYTES)
+        return fail(EVOXB_E_WORKSPACE,
+                    "evoxb_crowding_noalloc_f32: n = %lld, m = %d needs %zu bytes of scratch but the built-in array "
+                    "holds %u; use evoxb_crowding_f32 with a caller workspace for this size",
+                    (long long)n, m, need, (unsigned)EVOXB_NOALLOC_SCRATCH_BYTES);
+    void *scratch = nullptr;
+    if (int rc = noalloc_scratch_for_current_device(&scratch)) return rc;
+    // Nothing in the array has to start at zero: every word a call reads (segment length, tile
+    // counts, keys, indices, histograms, per-objective contributions) is written earlier in the
+    // same call, so the previous call's leftovers are never observed.
+    CrowdLayout L = crowd_layout(scratch, n, m);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    return launch_crowding(fitness, mask, n, m, dist, L, s);
 }
 
 }  // extern "C"

@@ -72,6 +72,29 @@ EVOXB_API int evoxb_crowding_workspace_bytes(int64_t n, int m, size_t *bytes);
 EVOXB_API int evoxb_crowding_f32(const float *fitness, const uint8_t *mask, int64_t n, int m, float *dist,
                                  void *ws, size_t ws_bytes, evoxb_stream_t stream);
 
+/* ---- crowding distance without any allocation (no counterpart in the reference) ---------------
+ * Some callers of this library cannot obtain device memory at the moment they need a result: a
+ * custom-call handler running inside a compiled step only owns the buffers its runtime handed it
+ * (a cudaMalloc there would stall every stream of the device and bypass the runtime's memory
+ * accounting), and a host loop that has committed all of its memory budget has nothing left to
+ * pass as a workspace.  For them this variant of evoxb_crowding_f32 keeps its sort buffers in an
+ * 8 MiB array that is part of the library itself; it takes no workspace and calls no cudaMalloc,
+ * cudaFree or other allocating routine.  Inputs, outputs and results are those of
+ * evoxb_crowding_f32.
+ *   - Limit: sizes whose evoxb_crowding_workspace_bytes() exceed EVOXB_CROWDING_NOALLOC_MAX_BYTES
+ *     (8 MiB: e.g. n = 65536 with m <= 6, n = 32768 with m <= 12) are rejected with
+ *     EVOXB_E_WORKSPACE and a message naming both numbers; nothing is launched.
+ *   - The first call on each device looks up the array's device address (with that device
+ *     current); make that first call before starting any stream capture on the device.
+ *   - Every GPU that loads the library holds the 8 MiB until the process exits.
+ *   - All calls on a device share the one array and it keeps the previous call's contents; each
+ *     call writes everything it later reads, so nothing needs clearing -- but two calls that
+ *     overlap on the GPU (different streams, or different host threads on the same device)
+ *     race on it.  Serialise them, or use evoxb_crowding_f32 with separate workspaces.          */
+#define EVOXB_CROWDING_NOALLOC_MAX_BYTES (8u << 20)
+EVOXB_API int evoxb_crowding_noalloc_f32(const float *fitness, const uint8_t *mask, int64_t n, int m,
+                                         float *dist, evoxb_stream_t stream);
+
 /* ---- a7: NSGA-II survivor selection ------------------------------------------------------------
  * src/evox/algorithms/mo/nsga2.py:90-96 (same block: gde3.py:88-97, im_moea.py:131-141):
  * rank = non_dominated_sort(fitness); worst_rank = rank[argsort(rank)[pop_size]];
