@@ -174,6 +174,138 @@ inline int launch_dominance_build(const float *xt, int64_t npad, int64_t row0, i
     return 0;
 }
 
+// ---- K1 (presorted population): upper-triangular build ------------------------------------------
+// Rows are in lexicographic order (presort.cuh), so D[i][j] = (uid_i < uid_j) & all_{k>=1}(x_ik <= x_jk):
+// M-1 float compares + 1 integer compare per pair instead of 2 M, and only tiles that reach above
+// the diagonal are computed.  Row tiles (128 rows) are grouped in bands of 32 (= one 4096-column
+// chunk); band b needs column tiles 4 b .. ntc-1.  Tiles of the diagonal chunk that lie entirely
+// left of their rows are written as zeros because the peel streams whole 512-byte chunks.
+struct TriGrid {
+    int ntc;     // column tiles (npad / 1024)
+    int nrt;     // row tiles of this launch
+    int nbands;  // ceil(nrt / 32)
+    long long total;
+};
+
+__host__ __device__ inline long long tri_tiles_before_band(int b, int ntc) {
+    return 32ll * ((long long)b * ntc - 2ll * b * (b - 1));
+}
+
+inline TriGrid make_tri_grid(int64_t npad, int64_t n_rows) {
+    TriGrid g;
+    g.ntc = (int)(npad / 1024);
+    g.nrt = (int)div_up(n_rows, 128);
+    g.nbands = (g.nrt + 31) / 32;
+    const int last = g.nbands - 1;
+    g.total = tri_tiles_before_band(last, g.ntc) + (long long)(g.nrt - 32 * last) * (g.ntc - 4 * last);
+    return g;
+}
+
+template <int M>
+__global__ void __launch_bounds__(kBuildThreads)
+dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows, const int *__restrict__ uid_row,
+                           const int *__restrict__ uid_col, uint32_t *__restrict__ D, int64_t row_words, TriGrid g) {
+    constexpr int K = (M > 1) ? (M - 1) : 1;  // objectives 1..M-1 are compared
+    __shared__ float xs[kTileRows][K];
+    __shared__ int us[kTileRows];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+
+    // tile id -> (band, row tile, column tile)
+    const long long t = blockIdx.x;
+    int lo = 0, hi = g.nbands;  // before(lo) <= t < before(hi)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (tri_tiles_before_band(mid, g.ntc) <= t) lo = mid; else hi = mid;
+    }
+    const int band = lo;
+    const int width = g.ntc - 4 * band;
+    const long long local = t - tri_tiles_before_band(band, g.ntc);
+    const int rt = 32 * band + (int)(local / width);
+    const int ct = 4 * band + (int)(local % width);
+
+    const int64_t tile_row0 = (int64_t)rt * kTileRows;
+    const int64_t tile_col0 = (int64_t)ct * kTileCols;
+    const int64_t col_base = tile_col0 + warp * (kC * 32);
+
+    if (tile_col0 + kTileCols - 1 <= tile_row0) {  // entirely on or left of the diagonal: all zero
+        for (int rb = 0; rb < kTileRows; rb += 32) {
+            const int64_t r = tile_row0 + rb + lane;
+            if (r < n_rows)
+                *reinterpret_cast<uint4 *>(D + r * row_words + (col_base >> 5)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        return;
+    }
+
+    for (int q = threadIdx.x; q < kTileRows * K; q += kBuildThreads) {
+        const int r = q / K, k = q - r * K;
+        xs[r][k] = (M > 1 && tile_row0 + r < n_rows) ? xt[(int64_t)(k + 1) * npad + tile_row0 + r]
+                                                      : __int_as_float(0x7fc00000);
+    }
+    for (int r = threadIdx.x; r < kTileRows; r += kBuildThreads)
+        us[r] = (tile_row0 + r < n_rows) ? uid_row[tile_row0 + r] : 0x7fffffff;
+    float xj[kC][K];
+    int uj[kC];
+#pragma unroll
+    for (int c = 0; c < kC; ++c) {
+        uj[c] = uid_col[col_base + c * 32 + lane];
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            xj[c][k] = (M > 1) ? xt[(int64_t)(k + 1) * npad + col_base + c * 32 + lane] : 0.0f;
+    }
+    __syncthreads();
+
+    for (int rb = 0; rb < kTileRows; rb += 32) {
+        uint32_t w[kC];
+#pragma unroll
+        for (int c = 0; c < kC; ++c) w[c] = 0u;
+#pragma unroll
+        for (int ii = 0; ii < 32; ++ii) {
+            float xi[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) xi[k] = xs[rb + ii][k];
+            const int ui = us[rb + ii];
+            const bool mine = (lane == ii);
+#pragma unroll
+            for (int c = 0; c < kC; ++c) {
+                bool p = ui < uj[c];
+                if (M > 1) {
+#pragma unroll
+                    for (int k = 0; k < K; ++k) p = p && (xi[k] <= xj[c][k]);
+                }
+                const uint32_t b = __ballot_sync(0xffffffffu, p);
+                if (mine) w[c] = b;
+            }
+        }
+        const int64_t r = tile_row0 + rb + lane;
+        if (r < n_rows)
+            *reinterpret_cast<uint4 *>(D + r * row_words + (col_base >> 5)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+inline int launch_dominance_build_tri(const float *xt, int64_t npad, int64_t n_rows, int m, const int *uid_row,
+                                      const int *uid_col, uint32_t *D, int64_t row_words, cudaStream_t s) {
+    if (n_rows <= 0) return 0;
+    const TriGrid g = make_tri_grid(npad, n_rows);
+    if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
+    const unsigned grid = (unsigned)g.total;
+#define EVOXB_TRI_CASE(MM)                                                                                     \
+    case MM:                                                                                                   \
+        dominance_build_tri_kernel<MM><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, uid_row, uid_col, D,   \
+                                                                      row_words, g);                           \
+        break;
+    switch (m) {
+        EVOXB_TRI_CASE(1) EVOXB_TRI_CASE(2) EVOXB_TRI_CASE(3) EVOXB_TRI_CASE(4) EVOXB_TRI_CASE(5) EVOXB_TRI_CASE(6)
+        EVOXB_TRI_CASE(7) EVOXB_TRI_CASE(8) EVOXB_TRI_CASE(9) EVOXB_TRI_CASE(10) EVOXB_TRI_CASE(11) EVOXB_TRI_CASE(12)
+        EVOXB_TRI_CASE(13) EVOXB_TRI_CASE(14) EVOXB_TRI_CASE(15) EVOXB_TRI_CASE(16)
+        default:
+            return fail(EVOXB_E_UNSUPPORTED, "presorted build supports m <= 16 (got %d)", m);
+    }
+#undef EVOXB_TRI_CASE
+    EVOXB_LAUNCH_CHECK("dominance_build_tri_kernel");
+    return 0;
+}
+
 // ---- a2: dense boolean relation between two different sets (utils/common.py:101-104) ----------
 // One thread per output byte, x row kept in registers via shared memory; small helper, not on the
 // N^2 hot path (the hot path never materialises bytes).

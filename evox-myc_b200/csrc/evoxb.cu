@@ -6,6 +6,7 @@
 #include "dominance.cuh"
 #include "peel.cuh"
 #include "sort.cuh"
+#include "presort.cuh"
 #include "crowding.cuh"
 #include "select.cuh"
 
@@ -17,18 +18,30 @@ unsigned long long g_launches = 0;
 struct NdsLayout {
     int64_t n, npad, row_words;
     int m, nchunks;
+    bool tri;  // presorted population, upper-triangular matrix (m <= 16); otherwise full matrix in input order
     float *xt;
     uint32_t *D;
     int *count;
     int *list;
     PeelCtrl *ctrl;
+    // presort state (tri only)
+    SortBufs sb;
+    int *perm;
+    int *hp;
+    uint8_t *nanrow;
+    int *tile_max;
+    int *uid_row;
+    int *uid_col;
     size_t bytes;
 };
+
+static bool nds_use_tri(int m) { return m <= 16; }
 
 static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows) {
     NdsLayout L{};
     L.n = n;
     L.m = m;
+    L.tri = nds_use_tri(m);
     L.npad = round_up(n > 0 ? n : 1, kColPad);
     L.row_words = L.npad / 32;
     L.nchunks = (int)(L.npad / kChunkCols);
@@ -37,6 +50,21 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows) {
     L.xt = c.take<float>((size_t)L.npad * (size_t)m);
     L.count = c.take<int>((size_t)L.npad);
     L.list = c.take<int>((size_t)L.npad);
+    if (L.tri) {
+        L.sb.cap = L.npad;
+        L.sb.tiles = (int)div_up(L.sb.cap, kSortTile);
+        for (int b = 0; b < 2; ++b) {
+            L.sb.keys[b] = c.take<uint32_t>((size_t)L.npad);
+            L.sb.vals[b] = c.take<uint32_t>((size_t)L.npad);
+        }
+        L.sb.hist = c.take<uint32_t>(sort_hist_words(L.sb.cap, 1));
+        L.perm = c.take<int>((size_t)L.npad);
+        L.hp = c.take<int>((size_t)L.npad);
+        L.nanrow = c.take<uint8_t>((size_t)L.npad);
+        L.tile_max = c.take<int>((size_t)div_up(L.npad, kPrepTile));
+        L.uid_row = c.take<int>((size_t)L.npad);
+        L.uid_col = c.take<int>((size_t)L.npad);
+    }
     L.D = c.take<uint32_t>((size_t)n_rows * (size_t)L.row_words);
     L.bytes = c.total();
     return L;
@@ -76,20 +104,45 @@ namespace evoxb {
 // Enqueues the whole ranking (K0..K3) on `s`.  `L` must come from nds_layout(ws, n, m, n).
 static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const NdsLayout &L, cudaStream_t s,
                    Profiler &prof) {
+    if (L.nchunks > kMaxChunks)
+        return fail(EVOXB_E_UNSUPPORTED, "n = %lld exceeds %d rows", (long long)n, kMaxChunks * kChunkCols);
     prof.mark("prep", s);
     EVOXB_CUDA(cudaMemsetAsync(L.ctrl, 0, sizeof(PeelCtrl), s));
     EVOXB_CUDA(cudaMemsetAsync(L.count, 0, sizeof(int) * (size_t)L.npad, s));
-    transpose_pad_kernel<<<(unsigned)div_up(L.npad, 256), 256, 0, s>>>(fitness, n, m, L.npad, L.xt);
-    EVOXB_LAUNCH_CHECK("transpose_pad_kernel");
-
-    prof.mark("dominance_build", s);
-    if (int rc = launch_dominance_build(L.xt, L.npad, 0, n, m, L.D, L.row_words, s)) return rc;
+    const int *perm = nullptr;
+    if (L.tri) {
+        // lexicographic order = stable LSD sorts from the last objective to the first
+        const unsigned gb = (unsigned)div_up(n, 256);
+        int cur = 0;
+        for (int k = m - 1; k >= 0; --k) {
+            lex_keys_kernel<<<gb, 256, 0, s>>>(fitness, n, m, k, k == m - 1 ? nullptr : L.sb.vals[cur], L.sb.keys[cur ^ 1],
+                                               L.sb.vals[cur ^ 1]);
+            EVOXB_LAUNCH_CHECK("lex_keys_kernel");
+            cur ^= 1;
+            if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 32, s, &cur)) return rc;
+        }
+        const unsigned gp = (unsigned)div_up(L.npad, kPrepTile);
+        sorted_gather_kernel<<<gp, 256, 0, s>>>(fitness, n, m, L.npad, L.sb.vals[cur], L.xt, L.perm, L.hp, L.nanrow,
+                                                L.tile_max);
+        EVOXB_LAUNCH_CHECK("sorted_gather_kernel");
+        uid_kernel<<<gp, 256, 0, s>>>(L.hp, L.nanrow, L.tile_max, L.npad, L.uid_row, L.uid_col);
+        EVOXB_LAUNCH_CHECK("uid_kernel");
+        perm = L.perm;
+        prof.mark("dominance_build", s);
+        if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.D, L.row_words, s)) return rc;
+    } else {
+        transpose_pad_kernel<<<(unsigned)div_up(L.npad, 256), 256, 0, s>>>(fitness, n, m, L.npad, L.xt);
+        EVOXB_LAUNCH_CHECK("transpose_pad_kernel");
+        prof.mark("dominance_build", s);
+        if (int rc = launch_dominance_build(L.xt, L.npad, 0, n, m, L.D, L.row_words, s)) return rc;
+    }
 
     int blocks = 0;
     if (int rc = peel_grid(&blocks)) return rc;
+    const int tri = L.tri ? 1 : 0;
 
     prof.mark("dominator_count", s);
-    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, L.count);
+    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, tri, L.count);
     EVOXB_LAUNCH_CHECK("dominator_count_kernel");
 
     prof.mark("peel", s);
@@ -98,12 +151,12 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         int64_t row_words = L.row_words;
         int nchunks = L.nchunks;
         int nn = (int)n;
+        int tri_arg = tri;
         int *count = L.count;
         int *rk = rank;
-        const int *perm = nullptr;
         int *list = L.list;
         PeelCtrl *ctrl = L.ctrl;
-        void *args[] = {&D, &row_words, &nchunks, &nn, &count, &rk, &perm, &list, &ctrl};
+        void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl};
         EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_persistent_kernel, dim3(blocks), dim3(kPeelThreads),
                                                args, 0, s));
         ++g_launches;

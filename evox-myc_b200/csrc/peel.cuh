@@ -28,11 +28,6 @@ constexpr int kPlanesWarp = 12;           // a warp accumulates at most 2^12 - 8
 constexpr int kPlanes = kPlanesWarp + 3;  // after adding the 8 warps of a CTA
 constexpr int kWarpRowsCap = (1 << kPlanesWarp) - kBatch;
 
-struct PeelCtrl {
-    int len[2];       // member count of the current / next front (double-buffered)
-    int fronts_done;  // number of fronts peeled (written at exit)
-    int pad;
-};
 
 // sum (low) and carry (high) of three bit-vectors
 __device__ __forceinline__ void csa(uint32_t &hi, uint32_t &lo, uint32_t a, uint32_t b, uint32_t c) {
@@ -65,11 +60,93 @@ struct PeelSmem {
     uint32_t fin[kPlanes][kChunkWords];              // CTA totals, plane-major
 };
 
-// Streams rows members[t0..t1) (or rows t0..t1 themselves when members == nullptr), restricted to
-// the 4096-column chunk `chunk`, and adds sign * (column sums) to count[].
-__device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_words, const int *__restrict__ members,
-                                 int64_t t0, int64_t t1, int chunk, int *__restrict__ count, int sign,
-                                 PeelSmem &sm) {
+// ---- work decomposition -----------------------------------------------------------------------
+// Positions are grouped in regions of 4096 (= one column chunk).  A front's members are stored
+// region-major: region r keeps its members (any order) in list[r * 4096 ...] and their number in
+// cnt[r].  For column chunk c only members that can have bits there are streamed:
+//   triangular matrix (presorted population): regions 0..c   (row i has no bits left of column i)
+//   full matrix:                               all regions
+// pc[r]  = number of members in regions < r          (prefix of cnt)
+// S[c]   = number of (chunk, member) segments in chunks < c
+// The segment space [0, S[nchunks]) is split evenly over the CTAs, chunk-major, so a CTA touches
+// at most two chunks when the grid has at least nchunks CTAs.
+constexpr int kMaxChunks = 512;  // N <= 2M rows; beyond that the matrix would not fit in HBM anyway
+
+struct PrefixSmem {
+    int pc[kMaxChunks + 1];
+    long long S[kMaxChunks + 1];
+};
+
+// cnt == nullptr: every row 0..n-1 is a member (dominator count, K2).
+__device__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n, bool tri, PrefixSmem &ps) {
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        constexpr int kPer = kMaxChunks / 32;  // 16 entries per lane
+        int v[kPer];
+        int run = 0;
+#pragma unroll
+        for (int e = 0; e < kPer; ++e) {
+            const int r = lane * kPer + e;
+            int c = 0;
+            if (r < nchunks) {
+                if (cnt) c = __ldcg(cnt + r);
+                else c = (int)max((int64_t)0, min((int64_t)kChunkCols, n - (int64_t)r * kChunkCols));
+            }
+            run += c;
+            v[e] = run;
+        }
+        int incl = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const int before = incl - run;
+        if (lane == 0) ps.pc[0] = 0;
+#pragma unroll
+        for (int e = 0; e < kPer; ++e) ps.pc[lane * kPer + e + 1] = before + v[e];
+        __syncwarp();
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        long long w[kPer];
+        long long lrun = 0;
+#pragma unroll
+        for (int e = 0; e < kPer; ++e) {
+            const int c = lane * kPer + e;
+            long long len = 0;
+            if (c < nchunks) len = tri ? (long long)(before + v[e]) : (long long)total;
+            lrun += len;
+            w[e] = lrun;
+        }
+        long long lincl = lrun;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long t = __shfl_up_sync(0xffffffffu, lincl, o);
+            if (lane >= o) lincl += t;
+        }
+        const long long lbefore = lincl - lrun;
+        if (lane == 0) ps.S[0] = 0;
+#pragma unroll
+        for (int e = 0; e < kPer; ++e) ps.S[lane * kPer + e + 1] = lbefore + w[e];
+    }
+    __syncthreads();
+}
+
+// Row index of member number t (in region-major order) -- binary search in pc[], then the list.
+__device__ __forceinline__ int member_row(const int *__restrict__ list, const PrefixSmem &ps, int nregions, int64_t t) {
+    if (!list) return (int)t;
+    int lo = 0, hi = nregions;  // pc[lo] <= t < pc[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if ((int64_t)ps.pc[mid] <= t) lo = mid; else hi = mid;
+    }
+    return __ldcg(list + (int64_t)lo * kChunkCols + (t - ps.pc[lo]));
+}
+
+// Streams members t0..t1 (region-major numbering) restricted to the 4096-column chunk `chunk` and
+// adds sign * (column sums) to count[].
+__device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_words, const int *__restrict__ list,
+                                 const PrefixSmem &ps, int nregions, int64_t t0, int64_t t1, int chunk,
+                                 int *__restrict__ count, int sign, PeelSmem &sm) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const uint4 *base = reinterpret_cast<const uint4 *>(D + (int64_t)chunk * kChunkWords) + lane;
@@ -83,18 +160,20 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
 #pragma unroll
             for (int p = 0; p < kPlanes; ++p) pl[s][p] = 0u;
 
-        // warp `warp` takes rows f0 + warp, f0 + warp + 8, ... in batches of kBatch
+        // warp `warp` takes members f0 + warp, f0 + warp + 8, ... in batches of kBatch
         for (int64_t t = f0 + warp; t < f1; t += (int64_t)kPeelWarps * kBatch) {
+            // lane b (< kBatch) resolves the row of the b-th member of the batch
+            int my_row = -1;
+            {
+                const int64_t tt = t + (int64_t)lane * kPeelWarps;
+                if (lane < kBatch && tt < f1) my_row = member_row(list, ps, nregions, tt);
+            }
             uint4 v[kBatch];
 #pragma unroll
             for (int b = 0; b < kBatch; ++b) {
-                const int64_t tt = t + (int64_t)b * kPeelWarps;
-                if (tt < f1) {
-                    const int64_t row = members ? (int64_t)__ldcg(members + tt) : tt;  // list is rewritten every front: L2 read
-                    v[b] = ldg_stream_v4(base + row * row_vec);
-                } else {
-                    v[b] = make_uint4(0u, 0u, 0u, 0u);
-                }
+                const int row = __shfl_sync(0xffffffffu, my_row, b);
+                if (row >= 0) v[b] = ldg_stream_v4(base + (int64_t)row * row_vec);
+                else v[b] = make_uint4(0u, 0u, 0u, 0u);
             }
             uint32_t w[kBatch];
 #pragma unroll
@@ -173,37 +252,47 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
     }
 }
 
-// Splits the (chunk, member) space evenly over the CTAs of the grid: CTA b owns the linear range
-// [b * total / G, (b + 1) * total / G) of segments ordered chunk-major, so a CTA touches at most
-// two chunks when G >= nchunks.
-__device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_words, int nchunks,
-                                 const int *__restrict__ members, int64_t nf, int *__restrict__ count, int sign,
+// One front (or, with list == nullptr, all rows): the caller has run build_prefix().
+__device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, bool tri,
+                                 const int *__restrict__ list, const PrefixSmem &ps, int *__restrict__ count, int sign,
                                  PeelSmem &sm) {
-    const int64_t total = (int64_t)nchunks * nf;
-    const int64_t s0 = total * blockIdx.x / gridDim.x;
-    const int64_t s1 = total * (blockIdx.x + 1) / gridDim.x;
-    int64_t s = s0;
+    const long long total = ps.S[nchunks];
+    const long long s0 = total * blockIdx.x / gridDim.x;
+    const long long s1 = total * (blockIdx.x + 1) / gridDim.x;
+    if (s0 >= s1) return;
+    int lo = 0, hi = nchunks;  // S[lo] <= s0 < S[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (ps.S[mid] <= s0) lo = mid; else hi = mid;
+    }
+    long long s = s0;
+    int chunk = lo;
     while (s < s1) {
-        const int chunk = (int)(s / nf);
-        const int64_t t0 = s - (int64_t)chunk * nf;
-        const int64_t t1 = min(nf, t0 + (s1 - s));
-        accumulate_chunk(D, row_words, members, t0, t1, chunk, count, sign, sm);
+        const long long len = ps.S[chunk + 1] - ps.S[chunk];
+        const long long t0 = s - ps.S[chunk];
+        const long long t1 = min(len, t0 + (s1 - s));
+        if (t1 > t0)
+            accumulate_chunk(D, row_words, list, ps, tri ? chunk + 1 : nchunks, t0, t1, chunk, count, sign, sm);
         s += t1 - t0;
+        ++chunk;
     }
 }
 
 // K2: count[j] += number of rows in [0, n_rows) that dominate j   (non_dominate.py:61)
 __global__ void __launch_bounds__(kPeelThreads)
-dominator_count_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int64_t n_rows,
+dominator_count_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int64_t n_rows, int tri,
                        int *__restrict__ count) {
     __shared__ PeelSmem sm;
-    accumulate_front(D, row_words, nchunks, nullptr, n_rows, count, +1, sm);
+    __shared__ PrefixSmem ps;
+    build_prefix(nullptr, nchunks, n_rows, tri != 0, ps);
+    accumulate_front(D, row_words, nchunks, tri != 0, nullptr, ps, count, +1, sm);
 }
 
 // Front detection: every j < n with count[j] == 0 joins the front, gets its rank, and drops to -1
-// for good (the reference's "count -= front" trick, non_dominate.py:103).
+// for good (the reference's "count -= front" trick, non_dominate.py:103).  Members are appended to
+// their region's slice of the list; a warp covers 32 consecutive positions, i.e. one region.
 __device__ void collect_front(int *__restrict__ count, int n, int r, int *__restrict__ rank,
-                              const int *__restrict__ perm, int *__restrict__ list, int *__restrict__ len) {
+                              const int *__restrict__ perm, int *__restrict__ list, int *__restrict__ cnt) {
     const int lane = threadIdx.x & 31;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t n32 = round_up(n, 32);
@@ -211,11 +300,12 @@ __device__ void collect_front(int *__restrict__ count, int n, int r, int *__rest
         const bool in = (j < n) && (__ldcg(count + j) == 0);  // count is updated by L2 atomics
         const uint32_t m = __ballot_sync(0xffffffffu, in);
         if (m) {
+            const int region = (int)(j >> 12);
             int base = 0;
-            if (lane == 0) base = atomicAdd(len, __popc(m));
+            if (lane == 0) base = atomicAdd(cnt + region, __popc(m));
             base = __shfl_sync(0xffffffffu, base, 0);
             if (in) {
-                list[base + __popc(m & ((1u << lane) - 1u))] = (int)j;
+                list[(int64_t)region * kChunkCols + base + __popc(m & ((1u << lane) - 1u))] = (int)j;
                 rank[perm ? perm[j] : j] = r;
                 count[j] = -1;
             }
@@ -223,32 +313,32 @@ __device__ void collect_front(int *__restrict__ count, int n, int r, int *__rest
     }
 }
 
+struct PeelCtrl {
+    int cnt[2][kMaxChunks];  // members per region of the current / next front (double-buffered)
+    int fronts_done;         // number of fronts peeled (written at exit)
+};
+
 // K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).
 __global__ void __launch_bounds__(kPeelThreads)
-peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n,
+peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri,
                        int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm,
                        int *__restrict__ list, PeelCtrl *__restrict__ ctrl) {
     __shared__ PeelSmem sm;
+    __shared__ PrefixSmem ps;
     cg::grid_group grid = cg::this_grid();
     int r = 0;
     for (;;) {
-        collect_front(count, n, r, rank, perm, list, &ctrl->len[r & 1]);
+        collect_front(count, n, r, rank, perm, list, ctrl->cnt[r & 1]);
         grid.sync();
-        const int nf = *((volatile int *)&ctrl->len[r & 1]);
-        if (nf == 0) break;  // non_dominate.py:76-78: while any(front)
-        if (blockIdx.x == 0 && threadIdx.x == 0) ctrl->len[(r + 1) & 1] = 0;
-        accumulate_front(D, row_words, nchunks, list, nf, count, -1, sm);
+        build_prefix(ctrl->cnt[r & 1], nchunks, n, tri != 0, ps);
+        if (ps.pc[nchunks] == 0) break;  // non_dominate.py:76-78: while any(front)
+        if (blockIdx.x == 0)
+            for (int c = threadIdx.x; c < nchunks; c += blockDim.x) ctrl->cnt[(r + 1) & 1][c] = 0;
+        accumulate_front(D, row_words, nchunks, tri != 0, list, ps, count, -1, sm);
         grid.sync();
         ++r;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) ctrl->fronts_done = r;
-}
-
-// ---- non-persistent pieces, used by the row-sharded multi-GPU path (host drives the loop) ----
-__global__ void __launch_bounds__(kPeelThreads)
-collect_front_kernel(int *__restrict__ count, int n, int r, int *__restrict__ rank, const int *__restrict__ perm,
-                     int *__restrict__ list, int *__restrict__ len) {
-    collect_front(count, n, r, rank, perm, list, len);
 }
 
 }  // namespace evoxb
