@@ -30,6 +30,13 @@ EXPORTS = [
     "evoxb_argsort_workspace_bytes",
     "evoxb_argsort_f32",
     "evoxb_gather_rows_f32",
+    "evoxb_comm_unique_id",
+    "evoxb_comm_create",
+    "evoxb_comm_destroy",
+    "evoxb_shard_plan",
+    "evoxb_nds_sharded_workspace_bytes",
+    "evoxb_nds_rank_sharded_f32",
+    "evoxb_nsga2_select_sharded_f32",
     "evoxb_profile_enable",
     "evoxb_profile_read",
     "evoxb_launch_count",
@@ -66,6 +73,14 @@ def lib() -> ctypes.CDLL:
         L.evoxb_argsort_workspace_bytes.argtypes = [i64, ctypes.POINTER(sz)]
         L.evoxb_argsort_f32.argtypes = [vp, i64, vp, vp, sz, vp]
         L.evoxb_gather_rows_f32.argtypes = [vp, i64, i64, vp, i64, vp, vp]
+        ip = ctypes.POINTER(ctypes.c_int)
+        L.evoxb_comm_unique_id.argtypes = [vp]
+        L.evoxb_comm_create.argtypes = [ctypes.c_char_p, i32, i32, ctypes.POINTER(vp)]
+        L.evoxb_comm_destroy.argtypes = [vp]
+        L.evoxb_shard_plan.argtypes = [i64, i32, i32, ip, ip, ip, ip]
+        L.evoxb_nds_sharded_workspace_bytes.argtypes = [i64, i32, i32, i32, ctypes.POINTER(sz)]
+        L.evoxb_nds_rank_sharded_f32.argtypes = [vp, i64, i32, vp, vp, sz, vp, vp]
+        L.evoxb_nsga2_select_sharded_f32.argtypes = [vp, i64, i32, i64, vp, vp, vp, vp, sz, vp, vp]
         L.evoxb_launch_count.restype = ctypes.c_ulonglong
         L.evoxb_profile_enable.argtypes = [i32]
         L.evoxb_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]

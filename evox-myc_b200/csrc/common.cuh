@@ -46,6 +46,14 @@ constexpr int kColPad = 4096;  // dominance rows are padded to a multiple of 409
 __host__ __device__ inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 __host__ __device__ inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// Which column chunks this GPU owns: global chunk of local chunk lc is first + lc * stride.
+// Single GPU: {0, 1, nchunks}.  Row-sharded^T multi-GPU: rank p of P owns chunks p, p+P, ... and
+// stores, for every row, only the words of its own chunks (row stride = nlocal * 128 words).
+struct ChunkMap {
+    int first, stride, nlocal;
+    __host__ __device__ int global(int lc) const { return first + lc * stride; }
+};
+
 // Bump allocator over the caller's workspace; every block is 256-byte aligned.
 struct Carver {
     char *base;

@@ -185,6 +185,8 @@ struct TriGrid {
     int nrt;     // row tiles of this launch
     int nbands;  // ceil(nrt / 32)
     long long total;
+    int sharded;  // 0: 1-D grid over the needed tiles of the whole matrix; 1: 2-D grid (local column tile, row tile)
+    ChunkMap cm;  // column chunks owned by this GPU (sharded only)
 };
 
 __host__ __device__ inline long long tri_tiles_before_band(int b, int ntc) {
@@ -198,6 +200,8 @@ inline TriGrid make_tri_grid(int64_t npad, int64_t n_rows) {
     g.nbands = (g.nrt + 31) / 32;
     const int last = g.nbands - 1;
     g.total = tri_tiles_before_band(last, g.ntc) + (long long)(g.nrt - 32 * last) * (g.ntc - 4 * last);
+    g.sharded = 0;
+    g.cm = ChunkMap{0, 1, g.ntc / 4};
     return g;
 }
 
@@ -211,28 +215,39 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
 
-    // tile id -> (band, row tile, column tile)
-    const long long t = blockIdx.x;
-    int lo = 0, hi = g.nbands;  // before(lo) <= t < before(hi)
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (tri_tiles_before_band(mid, g.ntc) <= t) lo = mid; else hi = mid;
+    int rt, ct;
+    int64_t word0;  // word offset of the tile's first column inside a (local) matrix row
+    if (g.sharded) {
+        const int lct = blockIdx.x, lc = lct >> 2, c = g.cm.global(lc);
+        rt = blockIdx.y;
+        if (c < (rt >> 5)) return;  // chunk entirely left of the rows' own chunk: never read by the peel
+        ct = c * 4 + (lct & 3);
+        word0 = (int64_t)lct * (kTileCols / 32);
+    } else {
+        // tile id -> (band, row tile, column tile)
+        const long long t = blockIdx.x;
+        int lo = 0, hi = g.nbands;  // before(lo) <= t < before(hi)
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (tri_tiles_before_band(mid, g.ntc) <= t) lo = mid; else hi = mid;
+        }
+        const int band = lo;
+        const int width = g.ntc - 4 * band;
+        const long long local = t - tri_tiles_before_band(band, g.ntc);
+        rt = 32 * band + (int)(local / width);
+        ct = 4 * band + (int)(local % width);
+        word0 = (int64_t)ct * (kTileCols / 32);
     }
-    const int band = lo;
-    const int width = g.ntc - 4 * band;
-    const long long local = t - tri_tiles_before_band(band, g.ntc);
-    const int rt = 32 * band + (int)(local / width);
-    const int ct = 4 * band + (int)(local % width);
 
     const int64_t tile_row0 = (int64_t)rt * kTileRows;
     const int64_t tile_col0 = (int64_t)ct * kTileCols;
     const int64_t col_base = tile_col0 + warp * (kC * 32);
+    const int64_t word_base = word0 + warp * kC;
 
     if (tile_col0 + kTileCols - 1 <= tile_row0) {  // entirely on or left of the diagonal: all zero
         for (int rb = 0; rb < kTileRows; rb += 32) {
             const int64_t r = tile_row0 + rb + lane;
-            if (r < n_rows)
-                *reinterpret_cast<uint4 *>(D + r * row_words + (col_base >> 5)) = make_uint4(0u, 0u, 0u, 0u);
+            if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = make_uint4(0u, 0u, 0u, 0u);
         }
         return;
     }
@@ -278,17 +293,26 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
             }
         }
         const int64_t r = tile_row0 + rb + lane;
-        if (r < n_rows)
-            *reinterpret_cast<uint4 *>(D + r * row_words + (col_base >> 5)) = make_uint4(w[0], w[1], w[2], w[3]);
+        if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = make_uint4(w[0], w[1], w[2], w[3]);
     }
 }
 
+// cm == nullptr: the whole matrix on one GPU.  Otherwise only the column chunks of *cm are built and a
+// matrix row holds cm->nlocal * 128 words.
 inline int launch_dominance_build_tri(const float *xt, int64_t npad, int64_t n_rows, int m, const int *uid_row,
-                                      const int *uid_col, uint32_t *D, int64_t row_words, cudaStream_t s) {
+                                      const int *uid_col, uint32_t *D, int64_t row_words, cudaStream_t s,
+                                      const ChunkMap *cm = nullptr) {
     if (n_rows <= 0) return 0;
-    const TriGrid g = make_tri_grid(npad, n_rows);
+    TriGrid g = make_tri_grid(npad, n_rows);
     if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
-    const unsigned grid = (unsigned)g.total;
+    dim3 grid((unsigned)g.total);
+    if (cm) {
+        g.sharded = 1;
+        g.cm = *cm;
+        if (cm->nlocal <= 0) return 0;
+        if (g.nrt > 65535) return fail(EVOXB_E_UNSUPPORTED, "too many row tiles (%d)", g.nrt);
+        grid = dim3((unsigned)(cm->nlocal * 4), (unsigned)g.nrt);
+    }
 #define EVOXB_TRI_CASE(MM)                                                                                     \
     case MM:                                                                                                   \
         dominance_build_tri_kernel<MM><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, uid_row, uid_col, D,   \

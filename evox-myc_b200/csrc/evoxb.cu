@@ -1,6 +1,10 @@
 // C-ABI entry points of libevoxb.so (see include/evoxb.h).  Hand-written sm_100a CUDA only:
 // no CPU fallback, no library kernels on the compute path.
+#include <dlfcn.h>
+
 #include <mutex>
+#include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 #include "dominance.cuh"
@@ -14,6 +18,21 @@ namespace evoxb {
 
 bool g_profile_enabled = false;
 unsigned long long g_launches = 0;
+
+struct NcclId {
+    char internal[128];  // == ncclUniqueId
+};
+
+}  // namespace evoxb
+
+// Opaque communicator handed out by evoxb_comm_create (one per process / GPU).
+struct evoxb_comm {
+    void *nccl = nullptr;  // ncclComm_t
+    int rank = 0, nranks = 1;
+    int *h_flags = nullptr;  // pinned host ints for the per-batch termination check
+};
+
+namespace evoxb {
 
 struct NdsLayout {
     int64_t n, npad, row_words;
@@ -32,19 +51,31 @@ struct NdsLayout {
     int *tile_max;
     int *uid_row;
     int *uid_col;
+    // multi-GPU (column chunks owned cyclically): nranks == 1 means the whole matrix lives here
+    ChunkMap cm;
+    int nranks, slice_chunks;
+    uint32_t *send_bits;  // [slice_chunks][128]
+    uint32_t *recv_bits;  // [nranks][slice_chunks][128]
+    int *totals;          // front sizes of the current batch of fronts
+    int *cnt;             // members per region of the current front
     size_t bytes;
 };
 
 static bool nds_use_tri(int m) { return m <= 16; }
 
-static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows) {
+constexpr int kFrontBatch = 4;  // fronts enqueued between two host checks of "front empty?" (multi-GPU)
+
+static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nranks = 1, int rank = 0) {
     NdsLayout L{};
     L.n = n;
     L.m = m;
     L.tri = nds_use_tri(m);
     L.npad = round_up(n > 0 ? n : 1, kColPad);
-    L.row_words = L.npad / 32;
     L.nchunks = (int)(L.npad / kChunkCols);
+    L.nranks = nranks;
+    L.slice_chunks = (int)div_up(L.nchunks, nranks);
+    L.cm = ChunkMap{rank, nranks, rank < L.nchunks ? (L.nchunks - rank + nranks - 1) / nranks : 0};
+    L.row_words = (nranks == 1) ? L.npad / 32 : (int64_t)(L.cm.nlocal > 0 ? L.cm.nlocal : 1) * kChunkWords;
     Carver c(ws);
     L.ctrl = c.take<PeelCtrl>(1);
     L.xt = c.take<float>((size_t)L.npad * (size_t)m);
@@ -64,6 +95,12 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows) {
         L.tile_max = c.take<int>((size_t)div_up(L.npad, kPrepTile));
         L.uid_row = c.take<int>((size_t)L.npad);
         L.uid_col = c.take<int>((size_t)L.npad);
+    }
+    if (nranks > 1) {
+        L.send_bits = c.take<uint32_t>((size_t)L.slice_chunks * kChunkWords);
+        L.recv_bits = c.take<uint32_t>((size_t)nranks * L.slice_chunks * kChunkWords);
+        L.totals = c.take<int>(64);
+        L.cnt = c.take<int>(kMaxChunks);
     }
     L.D = c.take<uint32_t>((size_t)n_rows * (size_t)L.row_words);
     L.bytes = c.total();
@@ -101,6 +138,28 @@ static int peel_grid(int *blocks) {
 
 namespace evoxb {
 
+// Lexicographic presort + sorted objective-major copy + uids (presort.cuh).  Deterministic, so
+// every GPU of a sharded run computes the same permutation on its own.
+static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &L, cudaStream_t s) {
+    // lexicographic order = stable LSD sorts from the last objective to the first
+    const unsigned gb = (unsigned)div_up(n, 256);
+    int cur = 0;
+    for (int k = m - 1; k >= 0; --k) {
+        lex_keys_kernel<<<gb, 256, 0, s>>>(fitness, n, m, k, k == m - 1 ? nullptr : L.sb.vals[cur], L.sb.keys[cur ^ 1],
+                                           L.sb.vals[cur ^ 1]);
+        EVOXB_LAUNCH_CHECK("lex_keys_kernel");
+        cur ^= 1;
+        if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 32, s, &cur)) return rc;
+    }
+    const unsigned gp = (unsigned)div_up(L.npad, kPrepTile);
+    sorted_gather_kernel<<<gp, 256, 0, s>>>(fitness, n, m, L.npad, L.sb.vals[cur], L.xt, L.perm, L.hp, L.nanrow,
+                                            L.tile_max);
+    EVOXB_LAUNCH_CHECK("sorted_gather_kernel");
+    uid_kernel<<<gp, 256, 0, s>>>(L.hp, L.nanrow, L.tile_max, L.npad, L.uid_row, L.uid_col);
+    EVOXB_LAUNCH_CHECK("uid_kernel");
+    return 0;
+}
+
 // Enqueues the whole ranking (K0..K3) on `s`.  `L` must come from nds_layout(ws, n, m, n).
 static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const NdsLayout &L, cudaStream_t s,
                    Profiler &prof) {
@@ -111,22 +170,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     EVOXB_CUDA(cudaMemsetAsync(L.count, 0, sizeof(int) * (size_t)L.npad, s));
     const int *perm = nullptr;
     if (L.tri) {
-        // lexicographic order = stable LSD sorts from the last objective to the first
-        const unsigned gb = (unsigned)div_up(n, 256);
-        int cur = 0;
-        for (int k = m - 1; k >= 0; --k) {
-            lex_keys_kernel<<<gb, 256, 0, s>>>(fitness, n, m, k, k == m - 1 ? nullptr : L.sb.vals[cur], L.sb.keys[cur ^ 1],
-                                               L.sb.vals[cur ^ 1]);
-            EVOXB_LAUNCH_CHECK("lex_keys_kernel");
-            cur ^= 1;
-            if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 32, s, &cur)) return rc;
-        }
-        const unsigned gp = (unsigned)div_up(L.npad, kPrepTile);
-        sorted_gather_kernel<<<gp, 256, 0, s>>>(fitness, n, m, L.npad, L.sb.vals[cur], L.xt, L.perm, L.hp, L.nanrow,
-                                                L.tile_max);
-        EVOXB_LAUNCH_CHECK("sorted_gather_kernel");
-        uid_kernel<<<gp, 256, 0, s>>>(L.hp, L.nanrow, L.tile_max, L.npad, L.uid_row, L.uid_col);
-        EVOXB_LAUNCH_CHECK("uid_kernel");
+        if (int rc = run_presort(fitness, n, m, L, s)) return rc;
         perm = L.perm;
         prof.mark("dominance_build", s);
         if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.D, L.row_words, s)) return rc;
@@ -142,7 +186,8 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     const int tri = L.tri ? 1 : 0;
 
     prof.mark("dominator_count", s);
-    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, tri, L.count);
+    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, tri, ChunkMap{0, 1, L.nchunks},
+                                                           L.count);
     EVOXB_LAUNCH_CHECK("dominator_count_kernel");
 
     prof.mark("peel", s);
@@ -160,6 +205,105 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_persistent_kernel, dim3(blocks), dim3(kPeelThreads),
                                                args, 0, s));
         ++g_launches;
+    }
+    return 0;
+}
+
+// ---- multi-GPU: NCCL (loaded at run time from the process, torch ships libnccl.so.2) --------------
+struct NcclApi {
+    void *handle = nullptr;
+    int (*GetUniqueId)(void *) = nullptr;
+    int (*CommInitRank)(void **, int, NcclId, int) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+
+static NcclApi &nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char *env = getenv("EVOXB_NCCL_LIB");
+        const char *names[] = {env, "libnccl.so.2", "libnccl.so"};
+        for (const char *nm : names) {
+            if (!nm) continue;
+            api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (api.handle) break;
+        }
+        if (!api.handle) return;
+        api.GetUniqueId = (int (*)(void *))dlsym(api.handle, "ncclGetUniqueId");
+        api.CommInitRank = (int (*)(void **, int, NcclId, int))dlsym(api.handle, "ncclCommInitRank");
+        api.CommDestroy = (int (*)(void *))dlsym(api.handle, "ncclCommDestroy");
+        api.AllGather = (int (*)(const void *, void *, size_t, int, void *, cudaStream_t))dlsym(api.handle, "ncclAllGather");
+        api.GetErrorString = (const char *(*)(int))dlsym(api.handle, "ncclGetErrorString");
+        api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GetErrorString;
+    });
+    return api;
+}
+
+#define EVOXB_NCCL(call)                                                                            \
+    do {                                                                                            \
+        int r__ = (call);                                                                           \
+        if (r__ != 0)                                                                               \
+            return ::evoxb::fail(EVOXB_E_NCCL, "%s failed at %s:%d: %s", #call, __FILE__, __LINE__, \
+                                 nccl_api().GetErrorString(r__));                                   \
+    } while (0)
+
+// Row-sharded^T ranking: every GPU presorts (same permutation everywhere), builds and keeps the
+// matrix columns of its own chunks for ALL rows, and owns count[] of those columns.  Per front the
+// GPUs exchange one bit per individual (ncclAllGather of N/8 bytes in total); no other traffic.
+// The host checks "front empty?" once per kFrontBatch fronts (one 4-byte-per-front D2H + stream sync).
+static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank, const NdsLayout &L, evoxb_comm *comm,
+                           cudaStream_t s, Profiler &prof) {
+    if (!L.tri) return fail(EVOXB_E_UNSUPPORTED, "the multi-GPU path supports m <= 16 (got %d)", m);
+    if (L.nchunks > kMaxChunks)
+        return fail(EVOXB_E_UNSUPPORTED, "n = %lld exceeds %d rows", (long long)n, kMaxChunks * kChunkCols);
+    NcclApi &nc = nccl_api();
+    prof.mark("prep", s);
+    EVOXB_CUDA(cudaMemsetAsync(L.count, 0, sizeof(int) * (size_t)L.npad, s));
+    if (int rc = run_presort(fitness, n, m, L, s)) return rc;
+
+    prof.mark("dominance_build", s);
+    if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.D, L.row_words, s, &L.cm)) return rc;
+
+    int blocks = 0;
+    if (int rc = peel_grid(&blocks)) return rc;
+    prof.mark("dominator_count", s);
+    if (L.cm.nlocal > 0) {
+        dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, 1, L.cm, L.count);
+        EVOXB_LAUNCH_CHECK("dominator_count_kernel");
+    }
+
+    prof.mark("peel", s);
+    const size_t slice_words = (size_t)L.slice_chunks * kChunkWords;
+    const unsigned detect_blocks = (unsigned)div_up((int64_t)(L.cm.nlocal > 0 ? L.cm.nlocal : 1) * kChunkWords * 32, 256);
+    int r = 0;
+    for (;;) {
+        EVOXB_CUDA(cudaMemsetAsync(L.totals, 0, sizeof(int) * kFrontBatch, s));
+        for (int b = 0; b < kFrontBatch; ++b) {
+            EVOXB_CUDA(cudaMemsetAsync(L.send_bits, 0, sizeof(uint32_t) * slice_words, s));
+            if (L.cm.nlocal > 0) {
+                front_detect_owned_kernel<<<detect_blocks, 256, 0, s>>>(L.count, (int)n, L.cm, L.send_bits);
+                EVOXB_LAUNCH_CHECK("front_detect_owned_kernel");
+            }
+            EVOXB_NCCL(nc.AllGather(L.send_bits, L.recv_bits, slice_words, /*ncclUint32*/ 3, comm->nccl, s));
+            front_expand_kernel<<<L.nchunks, kChunkWords, 0, s>>>(L.recv_bits, L.nranks, L.slice_chunks, L.nchunks, r + b,
+                                                                  rank, L.perm, L.list, L.cnt, L.totals + b);
+            EVOXB_LAUNCH_CHECK("front_expand_kernel");
+            if (L.cm.nlocal > 0) {
+                front_subtract_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, (int)n, 1, L.cm, L.list,
+                                                                      L.cnt, L.count);
+                EVOXB_LAUNCH_CHECK("front_subtract_kernel");
+            }
+        }
+        EVOXB_CUDA(cudaMemcpyAsync(comm->h_flags, L.totals, sizeof(int) * kFrontBatch, cudaMemcpyDeviceToHost, s));
+        EVOXB_CUDA(cudaStreamSynchronize(s));
+        bool done = false;
+        for (int b = 0; b < kFrontBatch; ++b) done = done || (comm->h_flags[b] == 0);  // identical on every GPU
+        r += kFrontBatch;
+        if (done) break;
+        if (r > n + kFrontBatch) return fail(EVOXB_E_CUDA, "front loop did not terminate");
     }
     return 0;
 }
@@ -196,7 +340,7 @@ static ArgsortLayout argsort_layout(void *ws, int64_t n) {
     return A;
 }
 
-static SelectLayout select_layout(void *ws, int64_t n, int m) {
+static SelectLayout select_layout(void *ws, int64_t n, int m, int nranks = 1, int rank = 0) {
     SelectLayout S{};
     Carver c(ws);
     const int64_t n1 = n > 0 ? n : 1;
@@ -219,7 +363,7 @@ static SelectLayout select_layout(void *ws, int64_t n, int m) {
     }
     {
         char *sub = c.take<char>(0);
-        S.nds = nds_layout(sub, n, m, n);
+        S.nds = nds_layout(sub, n, m, n, nranks, rank);
         c.take<char>(S.nds.bytes);
     }
     S.bytes = c.total();
@@ -334,7 +478,8 @@ EVOXB_API int evoxb_nsga2_select_workspace_bytes(int64_t n, int m, size_t *bytes
 // variant 1: operator non_dominate (non_dominate.py:181-195): k-th rank at index topk-1, and the
 //            secondary key is -argsort(crowding distance) taken positionally (the reference's quirk, :192-194).
 static int select_impl(int variant, const float *fitness, int64_t n, int m, int64_t pop_size, int32_t *order,
-                       int32_t *rank_out, float *crowd_out, void *ws, size_t ws_bytes, evoxb_stream_t stream) {
+                       int32_t *rank_out, float *crowd_out, void *ws, size_t ws_bytes, evoxb_stream_t stream,
+                       evoxb_comm *comm = nullptr) {
     if (int rc = check_common(fitness, n, m)) return rc;
     const int64_t kth = variant == 0 ? pop_size : pop_size - 1;
     // rank[order[kth]] must exist (nsga2.py:92 / non_dominate.py:190)
@@ -343,7 +488,7 @@ static int select_impl(int variant, const float *fitness, int64_t n, int m, int6
                     (long long)pop_size, (long long)n);
     if (!order && pop_size > 0) return fail(EVOXB_E_INVALID, "order is null");
     if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
-    SelectLayout S = select_layout(ws, n, m);
+    SelectLayout S = select_layout(ws, n, m, comm ? comm->nranks : 1, comm ? comm->rank : 0);
     if (ws_bytes < S.bytes)
         return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, S.bytes);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -351,7 +496,11 @@ static int select_impl(int variant, const float *fitness, int64_t n, int m, int6
     prof.begin();
     int *rank = rank_out ? rank_out : S.rank;
     float *crowd = crowd_out ? crowd_out : S.crowd_out;
-    if (int rc = run_nds(fitness, n, m, rank, S.nds, s, prof)) return rc;
+    if (comm) {
+        if (int rc = run_nds_sharded(fitness, n, m, rank, S.nds, comm, s, prof)) return rc;
+    } else {
+        if (int rc = run_nds(fitness, n, m, rank, S.nds, s, prof)) return rc;
+    }
 
     prof.mark("worst_rank", s);
     const unsigned gb = (unsigned)div_up(n, 256);
@@ -400,6 +549,91 @@ EVOXB_API int evoxb_nsga2_select_f32(const float *fitness, int64_t n, int m, int
 EVOXB_API int evoxb_non_dominate_select_f32(const float *fitness, int64_t n, int m, int64_t topk, int32_t *order, void *ws,
                                   size_t ws_bytes, evoxb_stream_t stream) {
     return select_impl(1, fitness, n, m, topk, order, nullptr, nullptr, ws, ws_bytes, stream);
+}
+
+EVOXB_API int evoxb_comm_unique_id(void *id128) {
+    if (!id128) return fail(EVOXB_E_INVALID, "id128 is null");
+    NcclApi &nc = nccl_api();
+    if (!nc.ok) return fail(EVOXB_E_NCCL, "libnccl.so.2 could not be loaded (set EVOXB_NCCL_LIB)");
+    EVOXB_NCCL(nc.GetUniqueId(id128));
+    return 0;
+}
+
+EVOXB_API int evoxb_comm_create(const void *id128, int rank, int nranks, evoxb_comm **out) {
+    if (!id128 || !out) return fail(EVOXB_E_INVALID, "null pointer");
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail(EVOXB_E_INVALID, "bad rank %d of %d", rank, nranks);
+    NcclApi &nc = nccl_api();
+    if (!nc.ok) return fail(EVOXB_E_NCCL, "libnccl.so.2 could not be loaded (set EVOXB_NCCL_LIB)");
+    evoxb_comm *c = new evoxb_comm();
+    c->rank = rank;
+    c->nranks = nranks;
+    NcclId id;
+    memcpy(id.internal, id128, sizeof(id.internal));
+    int r = nc.CommInitRank(&c->nccl, nranks, id, rank);
+    if (r != 0) {
+        delete c;
+        return fail(EVOXB_E_NCCL, "ncclCommInitRank failed: %s", nc.GetErrorString(r));
+    }
+    cudaError_t e = cudaHostAlloc((void **)&c->h_flags, sizeof(int) * 64, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        nc.CommDestroy(c->nccl);
+        delete c;
+        return fail(EVOXB_E_CUDA, "cudaHostAlloc failed: %s", cudaGetErrorString(e));
+    }
+    *out = c;
+    return 0;
+}
+
+EVOXB_API int evoxb_comm_destroy(evoxb_comm *comm) {
+    if (!comm) return 0;
+    if (comm->h_flags) cudaFreeHost(comm->h_flags);
+    if (comm->nccl) nccl_api().CommDestroy(comm->nccl);
+    delete comm;
+    return 0;
+}
+
+// Column chunks (4096 columns each) owned by `rank`: first, stride, count -- pure host arithmetic.
+EVOXB_API int evoxb_shard_plan(int64_t n, int rank, int nranks, int *first_chunk, int *chunk_stride, int *local_chunks,
+                     int *total_chunks) {
+    if (n < 0 || nranks < 1 || rank < 0 || rank >= nranks) return fail(EVOXB_E_INVALID, "bad arguments");
+    NdsLayout L = nds_layout(nullptr, n, 1, 0, nranks, rank);
+    if (first_chunk) *first_chunk = L.cm.first;
+    if (chunk_stride) *chunk_stride = L.cm.stride;
+    if (local_chunks) *local_chunks = L.cm.nlocal;
+    if (total_chunks) *total_chunks = L.nchunks;
+    return 0;
+}
+
+EVOXB_API int evoxb_nds_sharded_workspace_bytes(int64_t n, int m, int rank, int nranks, size_t *bytes) {
+    if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
+    if (int rc = check_common((const void *)1, n, m)) return rc;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail(EVOXB_E_INVALID, "bad rank %d of %d", rank, nranks);
+    *bytes = select_layout(nullptr, n, m, nranks, rank).bytes;
+    return 0;
+}
+
+EVOXB_API int evoxb_nds_rank_sharded_f32(const float *fitness, int64_t n, int m, int32_t *rank, void *ws, size_t ws_bytes,
+                               evoxb_comm *comm, evoxb_stream_t stream) {
+    if (int rc = check_common(fitness, n, m)) return rc;
+    if (!comm) return fail(EVOXB_E_INVALID, "comm is null");
+    if (n == 0) return 0;
+    if (!rank) return fail(EVOXB_E_INVALID, "rank is null");
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
+    SelectLayout S = select_layout(ws, n, m, comm->nranks, comm->rank);
+    if (ws_bytes < S.bytes) return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, S.bytes);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Profiler &prof = profiler();
+    prof.begin();
+    if (int rc = run_nds_sharded(fitness, n, m, rank, S.nds, comm, s, prof)) return rc;
+    prof.mark("end", s);
+    return 0;
+}
+
+EVOXB_API int evoxb_nsga2_select_sharded_f32(const float *fitness, int64_t n, int m, int64_t pop_size, int32_t *order,
+                                   int32_t *rank_out, float *crowd_out, void *ws, size_t ws_bytes, evoxb_comm *comm,
+                                   evoxb_stream_t stream) {
+    if (!comm) return fail(EVOXB_E_INVALID, "comm is null");
+    return select_impl(0, fitness, n, m, pop_size, order, rank_out, crowd_out, ws, ws_bytes, stream, comm);
 }
 
 EVOXB_API int evoxb_argsort_workspace_bytes(int64_t n, size_t *bytes) {

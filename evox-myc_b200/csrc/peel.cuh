@@ -78,7 +78,9 @@ struct PrefixSmem {
 };
 
 // cnt == nullptr: every row 0..n-1 is a member (dominator count, K2).
-__device__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n, bool tri, PrefixSmem &ps) {
+// S is built over the LOCAL chunks of `cm`.
+__device__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n, bool tri, ChunkMap cm,
+                             PrefixSmem &ps) {
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;
         constexpr int kPer = kMaxChunks / 32;  // 16 entries per lane
@@ -111,9 +113,9 @@ __device__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n
         long long lrun = 0;
 #pragma unroll
         for (int e = 0; e < kPer; ++e) {
-            const int c = lane * kPer + e;
+            const int lc = lane * kPer + e;
             long long len = 0;
-            if (c < nchunks) len = tri ? (long long)(before + v[e]) : (long long)total;
+            if (lc < cm.nlocal) len = tri ? (long long)ps.pc[cm.global(lc) + 1] : (long long)total;
             lrun += len;
             w[e] = lrun;
         }
@@ -145,11 +147,11 @@ __device__ __forceinline__ int member_row(const int *__restrict__ list, const Pr
 // Streams members t0..t1 (region-major numbering) restricted to the 4096-column chunk `chunk` and
 // adds sign * (column sums) to count[].
 __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_words, const int *__restrict__ list,
-                                 const PrefixSmem &ps, int nregions, int64_t t0, int64_t t1, int chunk,
+                                 const PrefixSmem &ps, int nregions, int64_t t0, int64_t t1, int local_chunk, int chunk,
                                  int *__restrict__ count, int sign, PeelSmem &sm) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const uint4 *base = reinterpret_cast<const uint4 *>(D + (int64_t)chunk * kChunkWords) + lane;
+    const uint4 *base = reinterpret_cast<const uint4 *>(D + (int64_t)local_chunk * kChunkWords) + lane;
     const int64_t row_vec = row_words >> 2;  // row stride in uint4
 
     for (int64_t f0 = t0; f0 < t1; f0 += (int64_t)kWarpRowsCap * kPeelWarps) {
@@ -253,39 +255,40 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
 }
 
 // One front (or, with list == nullptr, all rows): the caller has run build_prefix().
-__device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, bool tri,
+__device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, bool tri, ChunkMap cm,
                                  const int *__restrict__ list, const PrefixSmem &ps, int *__restrict__ count, int sign,
                                  PeelSmem &sm) {
-    const long long total = ps.S[nchunks];
+    const long long total = ps.S[cm.nlocal];
     const long long s0 = total * blockIdx.x / gridDim.x;
     const long long s1 = total * (blockIdx.x + 1) / gridDim.x;
     if (s0 >= s1) return;
-    int lo = 0, hi = nchunks;  // S[lo] <= s0 < S[hi]
+    int lo = 0, hi = cm.nlocal;  // S[lo] <= s0 < S[hi]
     while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
         if (ps.S[mid] <= s0) lo = mid; else hi = mid;
     }
     long long s = s0;
-    int chunk = lo;
+    int lc = lo;
     while (s < s1) {
-        const long long len = ps.S[chunk + 1] - ps.S[chunk];
-        const long long t0 = s - ps.S[chunk];
+        const long long len = ps.S[lc + 1] - ps.S[lc];
+        const long long t0 = s - ps.S[lc];
         const long long t1 = min(len, t0 + (s1 - s));
+        const int chunk = cm.global(lc);
         if (t1 > t0)
-            accumulate_chunk(D, row_words, list, ps, tri ? chunk + 1 : nchunks, t0, t1, chunk, count, sign, sm);
+            accumulate_chunk(D, row_words, list, ps, tri ? chunk + 1 : nchunks, t0, t1, lc, chunk, count, sign, sm);
         s += t1 - t0;
-        ++chunk;
+        ++lc;
     }
 }
 
 // K2: count[j] += number of rows in [0, n_rows) that dominate j   (non_dominate.py:61)
 __global__ void __launch_bounds__(kPeelThreads)
 dominator_count_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int64_t n_rows, int tri,
-                       int *__restrict__ count) {
+                       ChunkMap cm, int *__restrict__ count) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
-    build_prefix(nullptr, nchunks, n_rows, tri != 0, ps);
-    accumulate_front(D, row_words, nchunks, tri != 0, nullptr, ps, count, +1, sm);
+    build_prefix(nullptr, nchunks, n_rows, tri != 0, cm, ps);
+    accumulate_front(D, row_words, nchunks, tri != 0, cm, nullptr, ps, count, +1, sm);
 }
 
 // Front detection: every j < n with count[j] == 0 joins the front, gets its rank, and drops to -1
@@ -326,19 +329,89 @@ peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nc
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     cg::grid_group grid = cg::this_grid();
+    const ChunkMap cm{0, 1, nchunks};
     int r = 0;
     for (;;) {
         collect_front(count, n, r, rank, perm, list, ctrl->cnt[r & 1]);
         grid.sync();
-        build_prefix(ctrl->cnt[r & 1], nchunks, n, tri != 0, ps);
+        build_prefix(ctrl->cnt[r & 1], nchunks, n, tri != 0, cm, ps);
         if (ps.pc[nchunks] == 0) break;  // non_dominate.py:76-78: while any(front)
         if (blockIdx.x == 0)
             for (int c = threadIdx.x; c < nchunks; c += blockDim.x) ctrl->cnt[(r + 1) & 1][c] = 0;
-        accumulate_front(D, row_words, nchunks, tri != 0, list, ps, count, -1, sm);
+        accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm);
         grid.sync();
         ++r;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) ctrl->fronts_done = r;
+}
+
+// ---- multi-GPU pieces (host drives the front loop; one small all-gather per front) -------------
+// Ownership is by column chunk (the dominated index): a GPU keeps count[] for its own columns, so
+// dominator counts never cross GPUs; what every GPU needs from the others is only WHO is in the
+// current front -- one bit per individual.
+
+// Marks the front among this GPU's own columns: bit j of `bits` (region-major, 128 words per local
+// chunk) is set iff count[j] == 0; those counts drop to -1 (non_dominate.py:103).
+__global__ void __launch_bounds__(256)
+front_detect_owned_kernel(int *__restrict__ count, int n, ChunkMap cm, uint32_t *__restrict__ bits) {
+    const int lane = threadIdx.x & 31;
+    const int64_t words = (int64_t)cm.nlocal * kChunkWords;
+    const int64_t gw = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;  // one warp per word
+    if (gw >= words) return;
+    const int lc = (int)(gw / kChunkWords);
+    const int64_t j = (int64_t)cm.global(lc) * kChunkCols + (gw % kChunkWords) * 32 + lane;
+    const bool in = (j < n) && (count[j] == 0);
+    if (in) count[j] = -1;
+    const uint32_t m = __ballot_sync(0xffffffffu, in);
+    if (lane == 0) bits[gw] = m;
+}
+
+// Turns the gathered bitmask (P slices of `slice_chunks` local chunks each) into region-major member
+// lists, writes the members' rank and counts the front.  One CTA of 128 threads per global chunk.
+__global__ void __launch_bounds__(kChunkWords)
+front_expand_kernel(const uint32_t *__restrict__ gathered, int nranks, int slice_chunks, int nchunks, int r,
+                    int *__restrict__ rank, const int *__restrict__ perm, int *__restrict__ list,
+                    int *__restrict__ cnt, int *__restrict__ total) {
+    __shared__ int wsum[kChunkWords / 32];
+    const int c = blockIdx.x;
+    if (c >= nchunks) return;
+    const int owner = c % nranks, lc = c / nranks;
+    const uint32_t w = gathered[((int64_t)owner * slice_chunks + lc) * kChunkWords + threadIdx.x];
+    const int mine = __popc(w);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int before = incl - mine;
+    for (int q = 0; q < warp; ++q) before += wsum[q];
+    uint32_t rest = w;
+    int pos = before;
+    while (rest) {
+        const int b = __ffs(rest) - 1;
+        rest &= rest - 1;
+        const int j = c * kChunkCols + threadIdx.x * 32 + b;
+        list[(int64_t)c * kChunkCols + pos++] = j;
+        rank[perm ? perm[j] : j] = r;
+    }
+    if (threadIdx.x == kChunkWords - 1) {
+        cnt[c] = before + mine;
+        if (before + mine) atomicAdd(total, before + mine);
+    }
+}
+
+// Subtracts the rows of the current front from this GPU's columns.
+__global__ void __launch_bounds__(kPeelThreads)
+front_subtract_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri, ChunkMap cm,
+                      const int *__restrict__ list, const int *__restrict__ cnt, int *__restrict__ count) {
+    __shared__ PeelSmem sm;
+    __shared__ PrefixSmem ps;
+    build_prefix(cnt, nchunks, n, tri != 0, cm, ps);
+    accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm);
 }
 
 }  // namespace evoxb

@@ -1,0 +1,147 @@
+"""Multi-GPU environmental selection: one process per GPU, dominance matrix sharded by column chunk.
+
+The reference never shards this path (``tell`` is replicated on every device,
+src/evox/workflows/std_workflow.py:194, :341); this is new capability behind the same results.
+``torch.distributed`` is used for plumbing only -- to hand the 128-byte NCCL id from rank 0 to the
+others.  The exchange itself (one bit per individual per front) is an ``ncclAllGather`` issued by
+libevoxb.so on its own communicator, between its own kernels.
+
+``shard_plan`` / ``simulate_exchange`` are the host-side logic and run on CPU (the latter is the
+executable specification of the protocol, used by the world_size-2 gloo test with NumPy arrays).
+"""
+
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib, _runtime as rt
+
+CHUNK = 4096  # columns per chunk (csrc/peel.cuh: kChunkCols)
+FRONT_BATCH = 4  # fronts between two termination checks (csrc/evoxb.cu: kFrontBatch)
+
+
+def shard_plan(n: int, rank: int, nranks: int):
+    """(first_chunk, chunk_stride, local_chunks, total_chunks) of ``rank`` -- evoxb_shard_plan."""
+    L = _lib.lib()
+    a, b, c, d = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _lib.check(L.evoxb_shard_plan(n, rank, nranks, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c), ctypes.byref(d)))
+    return a.value, b.value, c.value, d.value
+
+
+def owned_columns(n: int, rank: int, nranks: int) -> np.ndarray:
+    first, stride, nlocal, _ = shard_plan(n, rank, nranks)
+    cols = [np.arange(c * CHUNK, min(n, (c + 1) * CHUNK)) for c in range(first, first + nlocal * stride, stride)]
+    return np.concatenate(cols) if cols else np.zeros(0, dtype=np.int64)
+
+
+def simulate_exchange(dominates_cols, n: int, rank: int, nranks: int, all_gather):
+    """The per-front protocol of ``run_nds_sharded`` on host arrays.
+
+    ``dominates_cols(cols) -> bool (n, len(cols))`` gives this rank's columns of the dominance matrix;
+    ``all_gather(bits) -> list of every rank's bits``.  Returns the full rank vector (identical on
+    every rank) and the number of exchange rounds.
+    """
+    first, stride, nlocal, nchunks = shard_plan(n, rank, nranks)
+    slice_chunks = -(-nchunks // nranks)
+    cols = owned_columns(n, rank, nranks)
+    d = dominates_cols(cols)
+    count = d.sum(axis=0).astype(np.int64)  # counts of OWN columns only: no reduction across ranks
+    ranks = np.zeros(n, dtype=np.int32)
+    r = 0
+    rounds = 0
+    while True:
+        sizes = []
+        for _ in range(FRONT_BATCH):
+            bits = np.zeros(slice_chunks * CHUNK, dtype=np.uint8)  # one entry per column slot of my slice
+            mine = count == 0
+            count[mine] = -1
+            lc = (cols // CHUNK - first) // stride
+            bits[lc[mine] * CHUNK + cols[mine] % CHUNK] = 1
+            gathered = all_gather(bits)
+            rounds += 1
+            members = []
+            for c in range(nchunks):  # front_expand_kernel: chunk c lives in slice c % P at slot c // P
+                sl = gathered[c % nranks][(c // nranks) * CHUNK : (c // nranks + 1) * CHUNK]
+                members.append(c * CHUNK + np.nonzero(sl)[0])
+            members = np.concatenate(members)
+            ranks[members] = r
+            sizes.append(len(members))
+            if len(members):
+                count -= np.where(count >= 0, d[members].sum(axis=0), 0)
+            r += 1
+        if min(sizes) == 0:
+            return ranks, rounds
+
+
+class ShardedSelector:
+    """Holds the NCCL communicator and workspace of one rank; all ranks must make the same calls."""
+
+    def __init__(self, n: int, m: int, device: torch.device | None = None):
+        import torch.distributed as dist
+
+        rt.require_cuda()
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed must be initialised (one process per GPU)")
+        self.rank, self.nranks = dist.get_rank(), dist.get_world_size()
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.n, self.m = n, m
+        L = _lib.lib()
+        backend = dist.get_backend()
+        id_dev = self.device if backend == "nccl" else torch.device("cpu")
+        idbuf = (ctypes.c_ubyte * 128)()
+        if self.rank == 0:
+            _lib.check(L.evoxb_comm_unique_id(idbuf))
+        t = torch.tensor(list(idbuf), dtype=torch.uint8, device=id_dev)
+        dist.broadcast(t, src=0)
+        raw = bytes(t.cpu().tolist())
+        self._comm = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(L.evoxb_comm_create(raw, self.rank, self.nranks, ctypes.byref(self._comm)))
+            need = ctypes.c_size_t()
+            _lib.check(L.evoxb_nds_sharded_workspace_bytes(n, m, self.rank, self.nranks, ctypes.byref(need)))
+            self._ws = torch.empty(need.value, dtype=torch.uint8, device=self.device)
+
+    def close(self):
+        if getattr(self, "_comm", None):
+            _lib.lib().evoxb_comm_destroy(self._comm)
+            self._comm = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def non_dominated_sort(self, x):
+        L = _lib.lib()
+        a = rt.Arg(x, torch.float32, "snds_x", device=self.device)
+        n, m = a.dev.shape
+        assert (n, m) == (self.n, self.m), "ShardedSelector was sized for another population"
+        rank = torch.empty((n,), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(L.evoxb_nds_rank_sharded_f32(a.dev.data_ptr(), n, m, rank.data_ptr(), self._ws.data_ptr(),
+                                                    self._ws.numel(), self._comm, rt.stream_ptr(self.device)))
+        return rt.give_back(rank, a, "snds_r")
+
+    def nsga2_select(self, merged_fitness, pop_size: int, return_details: bool = False):
+        L = _lib.lib()
+        f = rt.Arg(merged_fitness, torch.float32, "ssel_f", device=self.device)
+        n, m = f.dev.shape
+        assert (n, m) == (self.n, self.m), "ShardedSelector was sized for another population"
+        order = torch.empty((pop_size,), dtype=torch.int32, device=self.device)
+        rank = torch.empty((n,), dtype=torch.int32, device=self.device) if return_details else None
+        crowd = torch.empty((n,), dtype=torch.float32, device=self.device) if return_details else None
+        with torch.cuda.device(self.device):
+            _lib.check(
+                L.evoxb_nsga2_select_sharded_f32(f.dev.data_ptr(), n, m, pop_size, order.data_ptr(),
+                                                 rank.data_ptr() if rank is not None else None,
+                                                 crowd.data_ptr() if crowd is not None else None,
+                                                 self._ws.data_ptr(), self._ws.numel(), self._comm,
+                                                 rt.stream_ptr(self.device))
+            )
+        if return_details:
+            return (rt.give_back(order, f, "ssel_o"), rt.give_back(rank, f, "ssel_r"), rt.give_back(crowd, f, "ssel_c"))
+        return rt.give_back(order, f, "ssel_o")

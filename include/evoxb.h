@@ -124,6 +124,31 @@ EVOXB_API int evoxb_argsort_f32(const float *x, int64_t n, int32_t *idx, void *w
 EVOXB_API int evoxb_gather_rows_f32(const float *src, int64_t n, int64_t d, const int32_t *idx, int64_t k,
                                     float *dst, evoxb_stream_t stream);
 
+/* ---- e: multi-GPU ranking, one process per GPU (no counterpart in the reference, whose tell() is
+ * replicated on every device: src/evox/workflows/std_workflow.py:194, :341) ---------------------------
+ * The bit-packed dominance matrix is sharded by COLUMN chunk (4096 dominated individuals per chunk,
+ * chunks dealt cyclically to the ranks); every rank keeps all rows of its chunks and the dominator
+ * counts of its columns, so counts never cross GPUs.  Per front the ranks exchange one bit per
+ * individual (ncclAllGather, N/8 bytes in total).  Every rank receives the full rank vector.
+ * NCCL is loaded at run time (libnccl.so.2 of the process, or $EVOXB_NCCL_LIB).
+ *   evoxb_comm_unique_id : rank 0 makes the 128-byte NCCL id; the caller broadcasts it (any transport)
+ *   evoxb_comm_create    : collective; call with the GPU of this rank current
+ * The sharded entry points synchronise `stream` once per 4 fronts (termination check) and must be
+ * called by all ranks with the same arguments.  Supports m <= 16.                                   */
+typedef struct evoxb_comm evoxb_comm_t;
+EVOXB_API int evoxb_comm_unique_id(void *id128);
+EVOXB_API int evoxb_comm_create(const void *id128, int rank, int nranks, evoxb_comm_t **out);
+EVOXB_API int evoxb_comm_destroy(evoxb_comm_t *comm);
+EVOXB_API int evoxb_shard_plan(int64_t n, int rank, int nranks, int *first_chunk, int *chunk_stride,
+                               int *local_chunks, int *total_chunks);
+EVOXB_API int evoxb_nds_sharded_workspace_bytes(int64_t n, int m, int rank, int nranks, size_t *bytes);
+EVOXB_API int evoxb_nds_rank_sharded_f32(const float *fitness, int64_t n, int m, int32_t *rank, void *ws,
+                                         size_t ws_bytes, evoxb_comm_t *comm, evoxb_stream_t stream);
+/* evoxb_nsga2_select_f32 with the ranking sharded; the crowding / selection tail is replicated. */
+EVOXB_API int evoxb_nsga2_select_sharded_f32(const float *fitness, int64_t n, int m, int64_t pop_size,
+                                             int32_t *order, int32_t *rank_out, float *crowd_out, void *ws,
+                                             size_t ws_bytes, evoxb_comm_t *comm, evoxb_stream_t stream);
+
 /* ---- profiling hook (no counterpart in the reference) --------------------------------------
  * When enabled, every compute entry point brackets its stages with CUDA events on the caller's
  * stream.  evoxb_profile_read() synchronises those events and returns, for the LAST call made

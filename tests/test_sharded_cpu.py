@@ -1,0 +1,83 @@
+"""Host-side logic of the multi-GPU path on CPU: the shard plan, and the per-front exchange protocol
+run by two gloo ranks on NumPy arrays (the oracle supplies each rank's matrix columns)."""
+
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import helpers as h
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_shard_plan_partitions_every_chunk_once():
+    from evox_myc_b200 import sharded
+
+    for n in (1, 4096, 4097, 65536, 262144, 100000):
+        for nranks in (1, 2, 3, 4, 8):
+            seen = []
+            for r in range(nranks):
+                first, stride, nlocal, total = sharded.shard_plan(n, r, nranks)
+                assert total == -(-n // 4096) and stride == nranks and first == r
+                seen += list(range(first, first + nlocal * stride, stride))
+            assert sorted(seen) == list(range(total))
+            cols = np.concatenate([sharded.owned_columns(n, r, nranks) for r in range(nranks)])
+            assert sorted(cols.tolist()) == list(range(n))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, n, m, seed, out):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch
+    import torch.distributed as dist
+
+    from evox_myc_b200 import sharded
+    from oracle import nds_oracle
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import helpers
+
+    x = helpers.nasty(n, m, seed)
+
+    def dominates_cols(cols):
+        return nds_oracle.dominate_relation(x, x[cols])
+
+    def all_gather(bits):
+        t = torch.from_numpy(bits)
+        outs = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(outs, t)
+        return [o.numpy() for o in outs]
+
+    ranks, rounds = sharded.simulate_exchange(dominates_cols, n, rank, world, all_gather)
+    want = nds_oracle.non_dominated_sort(x)
+    out[rank] = (bool(np.array_equal(ranks, want)), rounds, int(want.max()) + 1)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,m", [(9000, 3), (5000, 2)])
+def test_exchange_protocol_two_gloo_ranks(n, m):
+    import torch.multiprocessing as mp
+
+    world = 2
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, port, n, m, 7, out), nprocs=world, join=True)
+    assert len(out) == world
+    for r in range(world):
+        ok, rounds, fronts = out[r]
+        assert ok, f"rank {r}: ranks differ from the oracle"
+        assert fronts < rounds <= fronts + 4  # stops within one batch after the first empty front

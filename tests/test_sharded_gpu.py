@@ -1,0 +1,85 @@
+"""GPU tests of the multi-GPU path.  World size 1 runs on the single-GPU box (same kernels, same host
+loop, a one-rank NCCL communicator); world size 2+ needs as many GPUs and is skipped otherwise."""
+
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import helpers as h
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, cases, out):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch
+    import torch.distributed as dist
+
+    import helpers
+    from evox_myc_b200 import sharded
+    from oracle import c_oracle
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl" if world > 1 else "gloo", rank=rank, world_size=world,
+                            **({"device_id": torch.device("cuda", rank)} if world > 1 else {}))
+    res = []
+    for kind, n, m, seed in cases:
+        x = getattr(helpers, kind)(n, m, seed)
+        sel = sharded.ShardedSelector(n, m, torch.device("cuda", rank))
+        r1 = sel.non_dominated_sort(x)
+        r2 = sel.non_dominated_sort(torch.from_numpy(x).cuda(rank)).cpu().numpy()  # second call, same workspace
+        pop = n // 2
+        order, rk, crowd = sel.nsga2_select(x, pop, return_details=True)
+        w_order, w_rank, w_crowd = c_oracle.nsga2_select(x, pop)
+        fin = np.isfinite(w_crowd)
+        ok = (np.array_equal(r1, w_rank) and np.array_equal(r2, w_rank) and np.array_equal(rk, w_rank)
+              and np.array_equal(order, w_order) and np.array_equal(np.isfinite(crowd), fin)
+              and np.allclose(crowd[fin], w_crowd[fin], rtol=1e-6, atol=0))
+        res.append((kind, n, m, bool(ok)))
+        sel.close()
+    out[rank] = res
+    dist.destroy_process_group()
+
+
+CASES = [("uniform", 5000, 3, 1), ("nasty", 9001, 4, 2), ("uniform", 20000, 2, 3), ("integer_grid", 12000, 3, 4),
+         ("uniform", 40000, 5, 5)]
+
+
+def _run(world):
+    import torch.multiprocessing as mp
+
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), CASES, out), nprocs=world, join=True)
+    assert len(out) == world
+    for r in range(world):
+        for kind, n, m, ok in out[r]:
+            assert ok, f"rank {r} of {world}: {kind} {n}x{m} differs from the oracle"
+
+
+def test_sharded_world_size_1():
+    _run(1)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_multi_gpu(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    _run(world)
