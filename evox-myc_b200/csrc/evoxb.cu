@@ -65,7 +65,8 @@ static bool nds_use_tri(int m) { return m <= 16; }
 
 constexpr int kFrontBatch = 4;  // fronts enqueued between two host checks of "front empty?" (multi-GPU)
 
-static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nranks = 1, int rank = 0) {
+static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nranks = 1, int rank = 0,
+                            bool sharded = false) {
     NdsLayout L{};
     L.n = n;
     L.m = m;
@@ -96,7 +97,7 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         L.uid_row = c.take<int>((size_t)L.npad);
         L.uid_col = c.take<int>((size_t)L.npad);
     }
-    if (nranks > 1) {
+    if (sharded) {
         L.send_bits = c.take<uint32_t>((size_t)L.slice_chunks * kChunkWords);
         L.recv_bits = c.take<uint32_t>((size_t)nranks * L.slice_chunks * kChunkWords);
         L.totals = c.take<int>(64);
@@ -340,7 +341,7 @@ static ArgsortLayout argsort_layout(void *ws, int64_t n) {
     return A;
 }
 
-static SelectLayout select_layout(void *ws, int64_t n, int m, int nranks = 1, int rank = 0) {
+static SelectLayout select_layout(void *ws, int64_t n, int m, int nranks = 1, int rank = 0, bool sharded = false) {
     SelectLayout S{};
     Carver c(ws);
     const int64_t n1 = n > 0 ? n : 1;
@@ -363,7 +364,7 @@ static SelectLayout select_layout(void *ws, int64_t n, int m, int nranks = 1, in
     }
     {
         char *sub = c.take<char>(0);
-        S.nds = nds_layout(sub, n, m, n, nranks, rank);
+        S.nds = nds_layout(sub, n, m, n, nranks, rank, sharded);
         c.take<char>(S.nds.bytes);
     }
     S.bytes = c.total();
@@ -488,7 +489,7 @@ static int select_impl(int variant, const float *fitness, int64_t n, int m, int6
                     (long long)pop_size, (long long)n);
     if (!order && pop_size > 0) return fail(EVOXB_E_INVALID, "order is null");
     if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
-    SelectLayout S = select_layout(ws, n, m, comm ? comm->nranks : 1, comm ? comm->rank : 0);
+    SelectLayout S = select_layout(ws, n, m, comm ? comm->nranks : 1, comm ? comm->rank : 0, comm != nullptr);
     if (ws_bytes < S.bytes)
         return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, S.bytes);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -608,7 +609,7 @@ EVOXB_API int evoxb_nds_sharded_workspace_bytes(int64_t n, int m, int rank, int 
     if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
     if (int rc = check_common((const void *)1, n, m)) return rc;
     if (nranks < 1 || rank < 0 || rank >= nranks) return fail(EVOXB_E_INVALID, "bad rank %d of %d", rank, nranks);
-    *bytes = select_layout(nullptr, n, m, nranks, rank).bytes;
+    *bytes = select_layout(nullptr, n, m, nranks, rank, true).bytes;
     return 0;
 }
 
@@ -619,7 +620,7 @@ EVOXB_API int evoxb_nds_rank_sharded_f32(const float *fitness, int64_t n, int m,
     if (n == 0) return 0;
     if (!rank) return fail(EVOXB_E_INVALID, "rank is null");
     if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
-    SelectLayout S = select_layout(ws, n, m, comm->nranks, comm->rank);
+    SelectLayout S = select_layout(ws, n, m, comm->nranks, comm->rank, true);
     if (ws_bytes < S.bytes) return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, S.bytes);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     Profiler &prof = profiler();
