@@ -139,19 +139,36 @@ static int peel_grid(int *blocks) {
 
 namespace evoxb {
 
-// Lexicographic presort + sorted objective-major copy + uids (presort.cuh).  Deterministic, so
+// Presort by (key_0, S') + sorted objective-major copy + uids (presort.cuh).  Deterministic, so
 // every GPU of a sharded run computes the same permutation on its own.
 static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &L, cudaStream_t s) {
-    // lexicographic order = stable LSD sorts from the last objective to the first
+    // order by (key_0, S'): stable LSD passes over S' (low 32 bits, then the few high bits), then key_0
     const unsigned gb = (unsigned)div_up(n, 256);
     int cur = 0;
-    for (int k = m - 1; k >= 0; --k) {
-        lex_keys_kernel<<<gb, 256, 0, s>>>(fitness, n, m, k, k == m - 1 ? nullptr : L.sb.vals[cur], L.sb.keys[cur ^ 1],
-                                           L.sb.vals[cur ^ 1]);
-        EVOXB_LAUNCH_CHECK("lex_keys_kernel");
-        cur ^= 1;
+    if (m > 1) {
+        presort_keys_sumlo_kernel<<<gb, 256, 0, s>>>(fitness, n, m, L.sb.keys[cur], L.sb.vals[cur]);
+        EVOXB_LAUNCH_CHECK("presort_keys_sumlo_kernel");
         if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 32, s, &cur)) return rc;
+        if (m > 2) {  // S' can exceed 32 bits only when it has at least two terms
+            presort_keys_gather_kernel<<<gb, 256, 0, s>>>(fitness, n, m, 0, L.sb.vals[cur], L.sb.keys[cur ^ 1],
+                                                          L.sb.vals[cur ^ 1]);
+            EVOXB_LAUNCH_CHECK("presort_keys_gather_kernel");
+            cur ^= 1;
+            if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 8, s, &cur)) return rc;
+        }
+        presort_keys_gather_kernel<<<gb, 256, 0, s>>>(fitness, n, m, 1, L.sb.vals[cur], L.sb.keys[cur ^ 1],
+                                                      L.sb.vals[cur ^ 1]);
+        EVOXB_LAUNCH_CHECK("presort_keys_gather_kernel");
+        cur ^= 1;
+    } else {
+        presort_keys_sumlo_kernel<<<gb, 256, 0, s>>>(fitness, n, 1, L.sb.keys[cur], L.sb.vals[cur]);  // identity perm
+        EVOXB_LAUNCH_CHECK("presort_keys_sumlo_kernel");
+        presort_keys_gather_kernel<<<gb, 256, 0, s>>>(fitness, n, m, 1, L.sb.vals[cur], L.sb.keys[cur ^ 1],
+                                                      L.sb.vals[cur ^ 1]);
+        EVOXB_LAUNCH_CHECK("presort_keys_gather_kernel");
+        cur ^= 1;
     }
+    if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 32, s, &cur)) return rc;
     const unsigned gp = (unsigned)div_up(L.npad, kPrepTile);
     sorted_gather_kernel<<<gp, 256, 0, s>>>(fitness, n, m, L.npad, L.sb.vals[cur], L.xt, L.perm, L.hp, L.nanrow,
                                             L.tile_max);

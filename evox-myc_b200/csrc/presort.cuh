@@ -1,14 +1,17 @@
-// Lexicographic presort of the population, so that the dominance matrix becomes strictly upper
-// triangular and one objective compare per pair disappears.
+// Presort of the population, so that the dominance matrix becomes strictly upper triangular and one
+// objective compare per pair disappears.
 //
 // No counterpart in the reference (its matrix at non_dominate.py:60 is built in input order).
-// Why it is exact: sort the rows lexicographically by (x_0, x_1, ..., x_{M-1}) with lax.sort's
-// float order (-0 == +0, NaN last).  If row a dominates row b then a <= b componentwise and
-// a != b, hence a is lexicographically smaller: a sits BEFORE b.  So in sorted positions
+// Rows are sorted by the pair (key_0, S') where key_k is the order-preserving u32 image of objective
+// k (lax.sort order: -0 == +0) and S' = sum_{k>=1} key_k as an exact integer (< 2^36 for M <= 16).
+// Why that is enough: if row a dominates row b then key_k(a) <= key_k(b) for every k with at least
+// one strict, hence (key_0, S') of a is lexicographically smaller: a sits BEFORE b, in a different
+// run of equal pairs.  Conversely, with uid = 1-based start position of a row's run of equal pairs,
 //     D[i][j] = (uid_i < uid_j) & all_{k>=1}(x_ik <= x_jk)
-// where uid is the 1-based position of the first row of a run of identical rows: i < j in
-// position already gives x_i0 <= x_j0, identical rows (which never dominate each other) share a
-// uid, and "componentwise <= and not identical" is exactly all(<=) & any(<) of common.py:98.
+// holds for ALL ordered pairs of NaN-free rows: uid_i < uid_j gives key_0(i) <= key_0(j), i.e.
+// x_i0 <= x_j0, which completes all(<=); and rows with all(<=) that are not identical have a strictly
+// smaller pair, while identical rows share a uid -- exactly all(<=) & any(<) of common.py:98.
+// The sort costs 9 radix passes whatever M is (a full lexicographic sort would need 4 M).
 // Rows holding a NaN never dominate and are never dominated (every compare with NaN is false):
 // they get uid_row = INT_MAX, uid_col = 0, which makes the uid test false in both roles.
 // Ranks are produced in sorted positions and written back through the permutation.
@@ -19,21 +22,38 @@
 
 namespace evoxb {
 
-// keys[p] = key of objective k of the row currently at position p; vals[p] = that row's index.
-__global__ void lex_keys_kernel(const float *__restrict__ x, int64_t n, int m, int k, const uint32_t *__restrict__ perm,
-                                uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+__device__ __forceinline__ unsigned long long sum_tail_keys(const float *__restrict__ row, int m) {
+    unsigned long long acc = 0ull;
+    for (int k = 1; k < m; ++k) acc += float_to_key(row[k]);
+    return acc;
+}
+
+// First sort key: low 32 bits of S'.  vals = identity.
+__global__ void presort_keys_sumlo_kernel(const float *__restrict__ x, int64_t n, int m, uint32_t *__restrict__ keys,
+                                          uint32_t *__restrict__ vals) {
     const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (p >= n) return;
-    const uint32_t row = perm ? perm[p] : (uint32_t)p;
-    keys[p] = float_to_key(x[(int64_t)row * m + k]);
+    keys[p] = (uint32_t)sum_tail_keys(x + p * m, m);
+    vals[p] = (uint32_t)p;
+}
+
+// which = 0: high bits of S' (bits 32..39); which = 1: key of objective 0.  Keys follow the
+// current permutation `perm`; vals = perm.
+__global__ void presort_keys_gather_kernel(const float *__restrict__ x, int64_t n, int m, int which,
+                                           const uint32_t *__restrict__ perm, uint32_t *__restrict__ keys,
+                                           uint32_t *__restrict__ vals) {
+    const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const uint32_t row = perm[p];
+    keys[p] = which == 0 ? (uint32_t)(sum_tail_keys(x + (int64_t)row * m, m) >> 32) : float_to_key(x[(int64_t)row * m]);
     vals[p] = row;
 }
 
 constexpr int kPrepTile = 4096;  // 256 threads x 16 positions
 
 // Gathers the sorted population into objective-major xt[k][p] (NaN padding past n), writes the
-// permutation as int, marks heads of runs of identical rows (hp[p] = p for a head, -1 otherwise),
-// flags NaN rows, and reduces the largest head position of every 4096-tile.
+// permutation as int, marks heads of runs of equal (key_0, S') pairs (hp[p] = p for a head, -1
+// otherwise), flags NaN rows, and reduces the largest head position of every 4096-tile.
 __global__ void __launch_bounds__(256)
 sorted_gather_kernel(const float *__restrict__ x, int64_t n, int m, int64_t npad, const uint32_t *__restrict__ perm_u,
                      float *__restrict__ xt, int *__restrict__ perm, int *__restrict__ hp, uint8_t *__restrict__ nanrow,
@@ -52,13 +72,16 @@ sorted_gather_kernel(const float *__restrict__ x, int64_t n, int m, int64_t npad
             continue;
         }
         const uint32_t row = perm_u[p];
-        const uint32_t prev = p > 0 ? perm_u[p - 1] : 0u;
-        bool differs = (p == 0), has_nan = false;
+        bool has_nan = false;
         for (int k = 0; k < m; ++k) {
             const float v = x[(int64_t)row * m + k];
             xt[(int64_t)k * npad + p] = v;
             has_nan = has_nan || (v != v);
-            if (p > 0) differs = differs || (v != x[(int64_t)prev * m + k]);  // NaN != anything: a head
+        }
+        bool differs = (p == 0);
+        if (p > 0) {
+            const float *a = x + (int64_t)row * m, *b = x + (int64_t)perm_u[p - 1] * m;
+            differs = float_to_key(a[0]) != float_to_key(b[0]) || sum_tail_keys(a, m) != sum_tail_keys(b, m);
         }
         perm[p] = (int)row;
         nanrow[p] = has_nan ? 1 : 0;
