@@ -212,6 +212,7 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     constexpr int K = (M > 1) ? (M - 1) : 1;  // objectives 1..M-1 are compared
     __shared__ float xs[kTileRows][K];
     __shared__ int us[kTileRows];
+    __shared__ __align__(16) uint32_t stage[kBuildThreads / 32][32][kC];  // per warp: 32 rows x 4 ballot words
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
 
@@ -270,31 +271,49 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     }
     __syncthreads();
 
-    for (int rb = 0; rb < kTileRows; rb += 32) {
-        uint32_t w[kC];
+    // If every row uid of the tile is below every column uid of this warp, the uid test is true for
+    // all of the warp's pairs and is dropped from the inner loop (the common case away from the
+    // diagonal; NaN rows / columns carry INT_MAX / 0 and force the full predicate).
+    int row_umax = max(max(us[lane], us[lane + 32]), max(us[lane + 64], us[lane + 96]));
+    int col_umin = min(min(uj[0], uj[1]), min(uj[2], uj[3]));
 #pragma unroll
-        for (int c = 0; c < kC; ++c) w[c] = 0u;
-#pragma unroll
-        for (int ii = 0; ii < 32; ++ii) {
-            float xi[K];
-#pragma unroll
-            for (int k = 0; k < K; ++k) xi[k] = xs[rb + ii][k];
-            const int ui = us[rb + ii];
-            const bool mine = (lane == ii);
-#pragma unroll
-            for (int c = 0; c < kC; ++c) {
-                bool p = ui < uj[c];
-                if (M > 1) {
-#pragma unroll
-                    for (int k = 0; k < K; ++k) p = p && (xi[k] <= xj[c][k]);
-                }
-                const uint32_t b = __ballot_sync(0xffffffffu, p);
-                if (mine) w[c] = b;
-            }
-        }
-        const int64_t r = tile_row0 + rb + lane;
-        if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = make_uint4(w[0], w[1], w[2], w[3]);
+    for (int o = 16; o > 0; o >>= 1) {
+        row_umax = max(row_umax, __shfl_xor_sync(0xffffffffu, row_umax, o));
+        col_umin = min(col_umin, __shfl_xor_sync(0xffffffffu, col_umin, o));
     }
+    const bool need_uid = !(row_umax < col_umin);
+    uint32_t(*st)[kC] = stage[warp];
+
+#define EVOXB_TRI_ROWS(WITH_UID)                                                                            \
+    for (int rb = 0; rb < kTileRows; rb += 32) {                                                            \
+        _Pragma("unroll") for (int ii = 0; ii < 32; ++ii) {                                                 \
+            float xi[K];                                                                                    \
+            _Pragma("unroll") for (int k = 0; k < K; ++k) xi[k] = xs[rb + ii][k];                           \
+            const int ui = WITH_UID ? us[rb + ii] : 0;                                                      \
+            uint32_t b[kC];                                                                                 \
+            _Pragma("unroll") for (int c = 0; c < kC; ++c) {                                                \
+                bool p = WITH_UID ? (ui < uj[c]) : true;                                                    \
+                if (M > 1) {                                                                                \
+                    _Pragma("unroll") for (int k = 0; k < K; ++k) p = p && (xi[k] <= xj[c][k]);             \
+                }                                                                                           \
+                b[c] = __ballot_sync(0xffffffffu, p);                                                       \
+            }                                                                                               \
+            /* the four words of row ii are warp-uniform: one lane parks them in shared memory */          \
+            if (lane == 0) *reinterpret_cast<uint4 *>(st[ii]) = make_uint4(b[0], b[1], b[2], b[3]);         \
+        }                                                                                                   \
+        __syncwarp();                                                                                       \
+        const uint4 v = *reinterpret_cast<const uint4 *>(st[lane]);                                         \
+        __syncwarp();                                                                                       \
+        const int64_t r = tile_row0 + rb + lane;                                                            \
+        if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = v;                      \
+    }
+
+    if (need_uid) {
+        EVOXB_TRI_ROWS(true)
+    } else {
+        EVOXB_TRI_ROWS(false)
+    }
+#undef EVOXB_TRI_ROWS
 }
 
 // cm == nullptr: the whole matrix on one GPU.  Otherwise only the column chunks of *cm are built and a
