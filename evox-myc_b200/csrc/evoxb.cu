@@ -89,11 +89,11 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
             L.sb.keys[b] = c.take<uint32_t>((size_t)L.npad);
             L.sb.vals[b] = c.take<uint32_t>((size_t)L.npad);
         }
-        L.sb.hist = c.take<uint32_t>(sort_hist_words(L.sb.cap, 1));
+        L.sb.hist = c.take<uint32_t>((size_t)kRadix * (size_t)div_up(L.npad, kCoopTile));
         L.perm = c.take<int>((size_t)L.npad);
         L.hp = c.take<int>((size_t)L.npad);
         L.nanrow = c.take<uint8_t>((size_t)L.npad);
-        L.tile_max = c.take<int>((size_t)div_up(L.npad, kPrepTile));
+        L.tile_max = c.take<int>((size_t)div_up(L.npad, kCoopTile));
         L.uid_row = c.take<int>((size_t)L.npad);
         L.uid_col = c.take<int>((size_t)L.npad);
     }
@@ -141,40 +141,43 @@ namespace evoxb {
 
 // Presort by (key_0, S') + sorted objective-major copy + uids (presort.cuh).  Deterministic, so
 // every GPU of a sharded run computes the same permutation on its own.
+static int presort_grid(int *blocks) {
+    static thread_local int cached_dev = -1, cached_blocks = 0;
+    int dev = 0;
+    EVOXB_CUDA(cudaGetDevice(&dev));
+    if (dev != cached_dev) {
+        int sms = 0, per_sm = 0;
+        EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, presort_coop_kernel, 256, 0));
+        if (per_sm < 1) return fail(EVOXB_E_CUDA, "presort kernel does not fit on an SM");
+        if (per_sm > 2) per_sm = 2;
+        cached_blocks = sms * per_sm;
+        cached_dev = dev;
+    }
+    *blocks = cached_blocks;
+    return 0;
+}
+
 static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &L, cudaStream_t s) {
     // order by (key_0, S'): stable LSD passes over S' (low 32 bits, then the few high bits), then key_0
-    const unsigned gb = (unsigned)div_up(n, 256);
-    int cur = 0;
+    PresortPasses pp{};
     if (m > 1) {
-        presort_keys_sumlo_kernel<<<gb, 256, 0, s>>>(fitness, n, m, L.sb.keys[cur], L.sb.vals[cur]);
-        EVOXB_LAUNCH_CHECK("presort_keys_sumlo_kernel");
-        if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 32, s, &cur)) return rc;
-        if (m > 2) {  // S' can exceed 32 bits only when it has at least two terms
-            presort_keys_gather_kernel<<<gb, 256, 0, s>>>(fitness, n, m, 0, L.sb.vals[cur], L.sb.keys[cur ^ 1],
-                                                          L.sb.vals[cur ^ 1]);
-            EVOXB_LAUNCH_CHECK("presort_keys_gather_kernel");
-            cur ^= 1;
-            if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 8, s, &cur)) return rc;
-        }
-        presort_keys_gather_kernel<<<gb, 256, 0, s>>>(fitness, n, m, 1, L.sb.vals[cur], L.sb.keys[cur ^ 1],
-                                                      L.sb.vals[cur ^ 1]);
-        EVOXB_LAUNCH_CHECK("presort_keys_gather_kernel");
-        cur ^= 1;
-    } else {
-        presort_keys_sumlo_kernel<<<gb, 256, 0, s>>>(fitness, n, 1, L.sb.keys[cur], L.sb.vals[cur]);  // identity perm
-        EVOXB_LAUNCH_CHECK("presort_keys_sumlo_kernel");
-        presort_keys_gather_kernel<<<gb, 256, 0, s>>>(fitness, n, m, 1, L.sb.vals[cur], L.sb.keys[cur ^ 1],
-                                                      L.sb.vals[cur ^ 1]);
-        EVOXB_LAUNCH_CHECK("presort_keys_gather_kernel");
-        cur ^= 1;
+        for (int sh = 0; sh < 32; sh += 8) { pp.kind[pp.count] = 0; pp.shift[pp.count++] = sh; }
+        if (m > 2) { pp.kind[pp.count] = 1; pp.shift[pp.count++] = 0; }  // S' exceeds 32 bits only with >= 2 terms
     }
-    if (int rc = radix_sort_pairs(L.sb, cur, 1, n, nullptr, 0, 32, s, &cur)) return rc;
-    const unsigned gp = (unsigned)div_up(L.npad, kPrepTile);
-    sorted_gather_kernel<<<gp, 256, 0, s>>>(fitness, n, m, L.npad, L.sb.vals[cur], L.xt, L.perm, L.hp, L.nanrow,
-                                            L.tile_max);
-    EVOXB_LAUNCH_CHECK("sorted_gather_kernel");
-    uid_kernel<<<gp, 256, 0, s>>>(L.hp, L.nanrow, L.tile_max, L.npad, L.uid_row, L.uid_col);
-    EVOXB_LAUNCH_CHECK("uid_kernel");
+    for (int sh = 0; sh < 32; sh += 8) { pp.kind[pp.count] = 2; pp.shift[pp.count++] = sh; }
+    int blocks = 0;
+    if (int rc = presort_grid(&blocks)) return rc;
+    const int tiles = (int)div_up(L.npad, kCoopTile);
+    if (blocks > tiles) blocks = tiles;
+    const float *x = fitness;
+    int nn = (int)n, mm = m, npad = (int)L.npad;
+    uint32_t *pa = L.sb.vals[0], *pb = L.sb.vals[1], *hist = L.sb.hist;
+    int *tile_max = L.tile_max, *hp = L.hp, *perm = L.perm, *ur = L.uid_row, *uc = L.uid_col;
+    float *xt = L.xt;
+    void *args[] = {&x, &nn, &mm, &npad, &pp, &pa, &pb, &hist, &tile_max, &hp, &xt, &perm, &ur, &uc};
+    EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)presort_coop_kernel, dim3(blocks), dim3(256), args, 0, s));
+    ++g_launches;
     return 0;
 }
 
