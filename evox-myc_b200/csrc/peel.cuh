@@ -55,9 +55,14 @@ __device__ __forceinline__ void vc_add8(uint32_t (&pl)[kPlanes], const uint32_t 
 }
 
 // Shared memory used by one CTA for the cross-warp reduction and the expansion.
+constexpr int kStageRows = 1024;  // member rows resolved per staging round
+
 struct PeelSmem {
     uint32_t xchg[kPeelWarps / 2][4 * kPlanes][32];  // up to 4 senders per round
-    uint32_t fin[kPlanes][kChunkWords];              // CTA totals, plane-major
+    union {
+        uint32_t fin[kPlanes][kChunkWords];          // CTA totals, plane-major (expansion)
+        int rows[kStageRows];                        // row ids of the members being streamed
+    };
 };
 
 // ---- work decomposition -----------------------------------------------------------------------
@@ -162,34 +167,35 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
 #pragma unroll
             for (int p = 0; p < kPlanes; ++p) pl[s][p] = 0u;
 
-        // warp `warp` takes members f0 + warp, f0 + warp + 8, ... in batches of kBatch
-        for (int64_t t = f0 + warp; t < f1; t += (int64_t)kPeelWarps * kBatch) {
-            // lane b (< kBatch) resolves the row of the b-th member of the batch
-            int my_row = -1;
-            {
-                const int64_t tt = t + (int64_t)lane * kPeelWarps;
-                if (lane < kBatch && tt < f1) my_row = member_row(list, ps, nregions, tt);
+        for (int64_t g0 = f0; g0 < f1; g0 += kStageRows) {
+            const int gn = (int)min((int64_t)kStageRows, f1 - g0);
+            // all threads resolve member -> row in parallel (one list-load latency per round)
+            for (int q = threadIdx.x; q < gn; q += kPeelThreads) sm.rows[q] = member_row(list, ps, nregions, g0 + q);
+            __syncthreads();
+            // warp `warp` takes staged members warp, warp + 8, ... in batches of kBatch
+            for (int q = warp; q < gn; q += kPeelWarps * kBatch) {
+                uint4 v[kBatch];
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) {
+                    const int qq = q + b * kPeelWarps;
+                    if (qq < gn) v[b] = ldg_stream_v4(base + (int64_t)sm.rows[qq] * row_vec);
+                    else v[b] = make_uint4(0u, 0u, 0u, 0u);
+                }
+                uint32_t w[kBatch];
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) w[b] = v[b].x;
+                vc_add8(pl[0], w);
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) w[b] = v[b].y;
+                vc_add8(pl[1], w);
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) w[b] = v[b].z;
+                vc_add8(pl[2], w);
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) w[b] = v[b].w;
+                vc_add8(pl[3], w);
             }
-            uint4 v[kBatch];
-#pragma unroll
-            for (int b = 0; b < kBatch; ++b) {
-                const int row = __shfl_sync(0xffffffffu, my_row, b);
-                if (row >= 0) v[b] = ldg_stream_v4(base + (int64_t)row * row_vec);
-                else v[b] = make_uint4(0u, 0u, 0u, 0u);
-            }
-            uint32_t w[kBatch];
-#pragma unroll
-            for (int b = 0; b < kBatch; ++b) w[b] = v[b].x;
-            vc_add8(pl[0], w);
-#pragma unroll
-            for (int b = 0; b < kBatch; ++b) w[b] = v[b].y;
-            vc_add8(pl[1], w);
-#pragma unroll
-            for (int b = 0; b < kBatch; ++b) w[b] = v[b].z;
-            vc_add8(pl[2], w);
-#pragma unroll
-            for (int b = 0; b < kBatch; ++b) w[b] = v[b].w;
-            vc_add8(pl[3], w);
+            __syncthreads();  // rows[] is reused by the next round and aliases fin[]
         }
 
         // ---- add the eight warps' bit-sliced counters (tree: 8 -> 4 -> 2 -> 1) ----
