@@ -8,7 +8,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(_HERE, "libevoxb.so")
+# EVOXB_LIB_PATH lets a developer load an experimental build; the product default is the in-tree .so
+LIB_PATH = os.environ.get("EVOXB_LIB_PATH") or os.path.join(_HERE, "libevoxb.so")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

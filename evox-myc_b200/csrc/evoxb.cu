@@ -124,7 +124,8 @@ static int peel_grid(int *blocks) {
     if (dev != cached_dev) {
         int sms = 0, per_sm = 0;
         EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peel_persistent_kernel, kPeelThreads, 0));
+        EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peel_persistent_kernel<kMaxChunks / 32>,
+                                                                 kPeelThreads, 0));
         if (per_sm < 1) return fail(EVOXB_E_CUDA, "peel kernel does not fit on an SM");
         if (per_sm > 3) per_sm = 3;
         cached_blocks = sms * per_sm;
@@ -223,8 +224,11 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         int *list = L.list;
         PeelCtrl *ctrl = L.ctrl;
         void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl};
-        EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_persistent_kernel, dim3(blocks), dim3(kPeelThreads),
-                                               args, 0, s));
+        // entries per lane of the region-prefix scan: 1 up to 32 chunks (N <= 131072), 4 up to 128, else 16
+        const void *kern = L.nchunks <= 32    ? (const void *)peel_persistent_kernel<1>
+                           : L.nchunks <= 128 ? (const void *)peel_persistent_kernel<4>
+                                              : (const void *)peel_persistent_kernel<kMaxChunks / 32>;
+        EVOXB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
     }
     return 0;

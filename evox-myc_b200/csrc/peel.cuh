@@ -82,25 +82,37 @@ struct PrefixSmem {
     long long S[kMaxChunks + 1];
 };
 
+// Order in which the local chunks are laid out in the segment space.  With a triangular matrix chunk
+// c carries (c + 1) / nchunks of the members, so small and large chunks alternate (0, last, 1,
+// last-1, ...): a CTA's share then never spans a run of tiny chunks (each chunk costs a flush).
+__device__ __forceinline__ int chunk_order(int i, int nlocal, bool tri) {
+    return tri ? ((i & 1) ? nlocal - 1 - (i >> 1) : (i >> 1)) : i;
+}
+
 // cnt == nullptr: every row 0..n-1 is a member (dominator count, K2).
-// S is built over the LOCAL chunks of `cm`.
-__device__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n, bool tri, ChunkMap cm,
-                             PrefixSmem &ps) {
+// pc[] is indexed by region; S[] by position in chunk_order() over the LOCAL chunks of `cm`.
+// kPer = entries per lane (compile-time: a run-time bound here makes ptxas keep ~100 extra registers
+// alive across the persistent front loop).
+template <int kPer>
+__device__ __forceinline__ void build_prefix_t(const int *__restrict__ cnt, int nchunks, int64_t n, bool tri, ChunkMap cm,
+                                               PrefixSmem &ps) {
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;
-        constexpr int kPer = kMaxChunks / 32;  // 16 entries per lane
+        constexpr int per = kPer;
         int v[kPer];
         int run = 0;
 #pragma unroll
         for (int e = 0; e < kPer; ++e) {
-            const int r = lane * kPer + e;
-            int c = 0;
-            if (r < nchunks) {
-                if (cnt) c = __ldcg(cnt + r);
-                else c = (int)max((int64_t)0, min((int64_t)kChunkCols, n - (int64_t)r * kChunkCols));
+            if (e < per) {
+                const int r = lane * per + e;
+                int c = 0;
+                if (r < nchunks) {
+                    if (cnt) c = __ldcg(cnt + r);
+                    else c = (int)max((int64_t)0, min((int64_t)kChunkCols, n - (int64_t)r * kChunkCols));
+                }
+                run += c;
+                v[e] = run;
             }
-            run += c;
-            v[e] = run;
         }
         int incl = run;
 #pragma unroll
@@ -111,18 +123,24 @@ __device__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n
         const int before = incl - run;
         if (lane == 0) ps.pc[0] = 0;
 #pragma unroll
-        for (int e = 0; e < kPer; ++e) ps.pc[lane * kPer + e + 1] = before + v[e];
+        for (int e = 0; e < kPer; ++e)
+            if (e < per) ps.pc[lane * per + e + 1] = before + v[e];
         __syncwarp();
         const int total = __shfl_sync(0xffffffffu, incl, 31);
+        constexpr int lper = kPer;
         long long w[kPer];
         long long lrun = 0;
 #pragma unroll
         for (int e = 0; e < kPer; ++e) {
-            const int lc = lane * kPer + e;
-            long long len = 0;
-            if (lc < cm.nlocal) len = tri ? (long long)ps.pc[cm.global(lc) + 1] : (long long)total;
-            lrun += len;
-            w[e] = lrun;
+            if (e < lper) {
+                const int i = lane * lper + e;
+                long long len = 0;
+                if (i < cm.nlocal)
+                    len = tri ? (long long)ps.pc[min(cm.global(chunk_order(i, cm.nlocal, true)), nchunks - 1) + 1]
+                              : (long long)total;
+                lrun += len;
+                w[e] = lrun;
+            }
         }
         long long lincl = lrun;
 #pragma unroll
@@ -133,9 +151,17 @@ __device__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n
         const long long lbefore = lincl - lrun;
         if (lane == 0) ps.S[0] = 0;
 #pragma unroll
-        for (int e = 0; e < kPer; ++e) ps.S[lane * kPer + e + 1] = lbefore + w[e];
+        for (int e = 0; e < kPer; ++e)
+            if (e < lper) ps.S[lane * lper + e + 1] = lbefore + w[e];
     }
     __syncthreads();
+}
+
+__device__ __forceinline__ void build_prefix(const int *__restrict__ cnt, int nchunks, int64_t n, bool tri, ChunkMap cm,
+                                             PrefixSmem &ps) {
+    if (nchunks <= 32) build_prefix_t<1>(cnt, nchunks, n, tri, cm, ps);        // N <= 131072
+    else if (nchunks <= 128) build_prefix_t<4>(cnt, nchunks, n, tri, cm, ps);  // N <= 524288
+    else build_prefix_t<kMaxChunks / 32>(cnt, nchunks, n, tri, cm, ps);
 }
 
 // Row index of member number t (in region-major order) -- binary search in pc[], then the list.
@@ -209,7 +235,8 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
 #pragma unroll
                 for (int s = 0; s < 4; ++s)
 #pragma unroll
-                    for (int p = 0; p < kPlanes; ++p) sm.xchg[slot][s * kPlanes + p][lane] = pl[s][p];
+                    for (int p = 0; p < kPlanes; ++p)
+                        sm.xchg[slot][s * kPlanes + p][lane] = pl[s][p];
             }
             __syncthreads();
             if (receiver) {
@@ -274,16 +301,17 @@ __device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_wor
         if (ps.S[mid] <= s0) lo = mid; else hi = mid;
     }
     long long s = s0;
-    int lc = lo;
+    int i = lo;  // position in chunk_order()
     while (s < s1) {
-        const long long len = ps.S[lc + 1] - ps.S[lc];
-        const long long t0 = s - ps.S[lc];
+        const long long len = ps.S[i + 1] - ps.S[i];
+        const long long t0 = s - ps.S[i];
         const long long t1 = min(len, t0 + (s1 - s));
+        const int lc = chunk_order(i, cm.nlocal, tri);
         const int chunk = cm.global(lc);
         if (t1 > t0)
             accumulate_chunk(D, row_words, list, ps, tri ? chunk + 1 : nchunks, t0, t1, lc, chunk, count, sign, sm);
         s += t1 - t0;
-        ++lc;
+        ++i;
     }
 }
 
@@ -328,6 +356,7 @@ struct PeelCtrl {
 };
 
 // K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).
+template <int kPer>
 __global__ void __launch_bounds__(kPeelThreads)
 peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri,
                        int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm,
@@ -340,7 +369,7 @@ peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nc
     for (;;) {
         collect_front(count, n, r, rank, perm, list, ctrl->cnt[r & 1]);
         grid.sync();
-        build_prefix(ctrl->cnt[r & 1], nchunks, n, tri != 0, cm, ps);
+        build_prefix_t<kPer>(ctrl->cnt[r & 1], nchunks, n, tri != 0, cm, ps);
         if (ps.pc[nchunks] == 0) break;  // non_dominate.py:76-78: while any(front)
         if (blockIdx.x == 0)
             for (int c = threadIdx.x; c < nchunks; c += blockDim.x) ctrl->cnt[(r + 1) & 1][c] = 0;
