@@ -33,6 +33,7 @@ EXPORTS = [
     "evoxb_comm_unique_id",
     "evoxb_comm_create",
     "evoxb_comm_destroy",
+    "evoxb_comm_status",
     "evoxb_shard_plan",
     "evoxb_nds_sharded_workspace_bytes",
     "evoxb_nds_rank_sharded_f32",
@@ -77,6 +78,7 @@ def lib() -> ctypes.CDLL:
         L.evoxb_comm_unique_id.argtypes = [vp]
         L.evoxb_comm_create.argtypes = [ctypes.c_char_p, i32, i32, ctypes.POINTER(vp)]
         L.evoxb_comm_destroy.argtypes = [vp]
+        L.evoxb_comm_status.argtypes = [vp, ip, ip, ip]
         L.evoxb_shard_plan.argtypes = [i64, i32, i32, ip, ip, ip, ip]
         L.evoxb_nds_sharded_workspace_bytes.argtypes = [i64, i32, i32, i32, ctypes.POINTER(sz)]
         L.evoxb_nds_rank_sharded_f32.argtypes = [vp, i64, i32, vp, vp, sz, vp, vp]

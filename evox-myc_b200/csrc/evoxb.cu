@@ -3,6 +3,7 @@
 #include <dlfcn.h>
 
 #include <mutex>
+#include <vector>
 #include <cstdlib>
 #include <cstring>
 
@@ -30,6 +31,12 @@ struct evoxb_comm {
     void *nccl = nullptr;  // ncclComm_t
     int rank = 0, nranks = 1;
     int *h_flags = nullptr;  // pinned host ints for the per-batch termination check
+    // peer-memory exchange (CUDA IPC); when it cannot be set up the NCCL all-gather path is used
+    bool p2p = false;
+    unsigned char *xbuf = nullptr;        // this rank's exchange buffer (cudaMalloc, exported to the peers)
+    unsigned char *peer_ptr[16] = {};     // peers' exchange buffers mapped into this process
+    unsigned char **peers_dev = nullptr;  // the same pointers in device memory, for the kernel
+    int *fronts_dev = nullptr;            // fronts peeled by the last call (device int)
 };
 
 namespace evoxb {
@@ -126,6 +133,10 @@ static int peel_grid(int *blocks) {
         EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peel_persistent_kernel<kMaxChunks / 32>,
                                                                  kPeelThreads, 0));
+        int per_sm_p2p = 0;
+        EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_p2p, peel_p2p_kernel<kMaxChunks / 32>,
+                                                                 kPeelThreads, 0));
+        if (per_sm_p2p < per_sm) per_sm = per_sm_p2p;  // one grid size serves both cooperative kernels
         if (per_sm < 1) return fail(EVOXB_E_CUDA, "peel kernel does not fit on an SM");
         if (per_sm > 3) per_sm = 3;
         cached_blocks = sms * per_sm;
@@ -302,6 +313,25 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
 
     prof.mark("peel", s);
     const size_t slice_words = (size_t)L.slice_chunks * kChunkWords;
+    if (comm->p2p && (size_t)L.nranks * slice_words <= (size_t)kXchgSliceWordsCap) {
+        // fused path: one persistent kernel per GPU exchanges the front bitmask over peer memory
+        EVOXB_CUDA(cudaMemsetAsync(L.send_bits, 0, sizeof(uint32_t) * slice_words, s));
+        const uint32_t *D = L.D;
+        int64_t row_words = L.row_words;
+        int nchunks = L.nchunks, nn = (int)n;
+        ChunkMap cm = L.cm;
+        int *count = L.count, *rk = rank, *list = L.list, *cnt = L.cnt, *fronts = comm->fronts_dev;
+        const int *perm = L.perm;
+        uint32_t *mybits = L.send_bits;
+        XchgCtx x{comm->peers_dev, comm->rank, comm->nranks, L.slice_chunks};
+        void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &mybits, &x, &fronts};
+        const void *kern = L.nchunks <= 32    ? (const void *)peel_p2p_kernel<1>
+                           : L.nchunks <= 128 ? (const void *)peel_p2p_kernel<4>
+                                              : (const void *)peel_p2p_kernel<kMaxChunks / 32>;
+        EVOXB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
+        ++g_launches;
+        return 0;
+    }
     const unsigned detect_blocks = (unsigned)div_up((int64_t)(L.cm.nlocal > 0 ? L.cm.nlocal : 1) * kChunkWords * 32, 256);
     int r = 0;
     for (;;) {
@@ -331,6 +361,68 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         if (r > n + kFrontBatch) return fail(EVOXB_E_CUDA, "front loop did not terminate");
     }
     return 0;
+}
+
+// Maps every rank's exchange buffer into this process (CUDA IPC over NVLink peer access).  Handles
+// travel through one ncclAllGather.  Any failure leaves comm->p2p == false (NCCL path); the decision
+// is made collectively so that all ranks take the same path.
+static void setup_peer_exchange(evoxb_comm *c) {
+    NcclApi &nc = nccl_api();
+    const int P = c->nranks;
+    if (P > kXchgMaxRanks || getenv("EVOXB_NO_P2P")) return;
+    cudaStream_t s = nullptr;
+    bool ok = true;
+    unsigned char *hbuf_dev = nullptr;
+    struct Slot { cudaIpcMemHandle_t h; int ok; int pad[15]; };
+    static_assert(sizeof(Slot) == 128, "slot size");
+    Slot mine{};
+    std::vector<Slot> all((size_t)P);
+    ok = ok && cudaMalloc((void **)&c->xbuf, xchg_buffer_bytes()) == cudaSuccess;
+    ok = ok && cudaMemset(c->xbuf, 0, xchg_buffer_bytes()) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&c->fronts_dev, sizeof(int)) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&c->peers_dev, sizeof(unsigned char *) * kXchgMaxRanks) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&hbuf_dev, sizeof(Slot) * (size_t)(P + 1)) == cudaSuccess;
+    if (ok && P > 1) ok = cudaIpcGetMemHandle(&mine.h, c->xbuf) == cudaSuccess;
+    mine.ok = ok ? 1 : 0;
+    if (hbuf_dev) {
+        // collective: everybody takes part even if its own setup failed, so nobody hangs
+        cudaMemcpy(hbuf_dev + sizeof(Slot) * (size_t)P, &mine, sizeof(Slot), cudaMemcpyHostToDevice);
+        int r = nc.AllGather(hbuf_dev + sizeof(Slot) * (size_t)P, hbuf_dev, sizeof(Slot), /*ncclUint8*/ 1, c->nccl, s);
+        cudaError_t e = cudaStreamSynchronize(s);
+        if (r != 0 || e != cudaSuccess) ok = false;
+        else cudaMemcpy(all.data(), hbuf_dev, sizeof(Slot) * (size_t)P, cudaMemcpyDeviceToHost);
+    }
+    for (int q = 0; ok && q < P; ++q) ok = all[(size_t)q].ok == 1;
+    for (int q = 0; ok && q < P; ++q) {
+        if (q == c->rank) {
+            c->peer_ptr[q] = c->xbuf;
+        } else {
+            void *ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&ptr, all[(size_t)q].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                ok = false;
+                cudaGetLastError();
+            }
+            c->peer_ptr[q] = static_cast<unsigned char *>(ptr);
+        }
+    }
+    // second collective round: the fused path is used only if EVERY rank mapped every peer
+    if (hbuf_dev) {
+        mine.ok = ok ? 1 : 0;
+        cudaMemcpy(hbuf_dev + sizeof(Slot) * (size_t)P, &mine, sizeof(Slot), cudaMemcpyHostToDevice);
+        int r = nc.AllGather(hbuf_dev + sizeof(Slot) * (size_t)P, hbuf_dev, sizeof(Slot), 1, c->nccl, s);
+        cudaError_t e = cudaStreamSynchronize(s);
+        if (r != 0 || e != cudaSuccess) ok = false;
+        else {
+            cudaMemcpy(all.data(), hbuf_dev, sizeof(Slot) * (size_t)P, cudaMemcpyDeviceToHost);
+            for (int q = 0; q < P; ++q) ok = ok && all[(size_t)q].ok == 1;
+        }
+        cudaFree(hbuf_dev);
+    } else {
+        ok = false;
+    }
+    if (ok) ok = cudaMemcpy(c->peers_dev, c->peer_ptr, sizeof(unsigned char *) * kXchgMaxRanks, cudaMemcpyHostToDevice) == cudaSuccess;
+    cudaGetLastError();
+    c->p2p = ok;
 }
 
 struct SelectLayout {
@@ -605,13 +697,33 @@ EVOXB_API int evoxb_comm_create(const void *id128, int rank, int nranks, evoxb_c
         delete c;
         return fail(EVOXB_E_CUDA, "cudaHostAlloc failed: %s", cudaGetErrorString(e));
     }
+    setup_peer_exchange(c);  // best effort: c->p2p says whether the fused path is available
     *out = c;
+    return 0;
+}
+
+EVOXB_API int evoxb_comm_status(evoxb_comm *comm, int *p2p_enabled, int *error, int *fronts) {
+    if (!comm) return fail(EVOXB_E_INVALID, "comm is null");
+    if (p2p_enabled) *p2p_enabled = comm->p2p ? 1 : 0;
+    if (error) *error = 0;
+    if (fronts) *fronts = 0;
+    if (comm->p2p) {
+        XchgHeader h;
+        EVOXB_CUDA(cudaMemcpy(&h, comm->xbuf, sizeof(h), cudaMemcpyDeviceToHost));
+        if (error) *error = (int)h.error;
+        if (fronts) EVOXB_CUDA(cudaMemcpy(fronts, comm->fronts_dev, sizeof(int), cudaMemcpyDeviceToHost));
+    }
     return 0;
 }
 
 EVOXB_API int evoxb_comm_destroy(evoxb_comm *comm) {
     if (!comm) return 0;
     if (comm->h_flags) cudaFreeHost(comm->h_flags);
+    for (int q = 0; q < comm->nranks && q < 16; ++q)
+        if (q != comm->rank && comm->peer_ptr[q]) cudaIpcCloseMemHandle(comm->peer_ptr[q]);
+    if (comm->peers_dev) cudaFree(comm->peers_dev);
+    if (comm->fronts_dev) cudaFree(comm->fronts_dev);
+    if (comm->xbuf) cudaFree(comm->xbuf);
     if (comm->nccl) nccl_api().CommDestroy(comm->nccl);
     delete comm;
     return 0;

@@ -449,4 +449,155 @@ front_subtract_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nch
     accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm);
 }
 
+// ---- multi-GPU, fused: the front loop and its exchange in ONE persistent kernel per GPU ---------------
+// Instead of three launches and an ncclAllGather per front, every GPU runs one cooperative kernel for
+// the whole peel.  Per front it marks the front among its own columns, block 0 stores that slice of
+// the bitmask straight into every peer's exchange buffer over NVLink (peer pointers obtained through
+// CUDA IPC at communicator creation), raises a per-sender epoch flag on each peer, and all CTAs wait
+// for the flags of all senders in local memory.  The exchange buffer is double-buffered by epoch
+// parity: a sender can be at most one front ahead of the slowest reader, because it needs that
+// reader's slice of the next front to go further.  Epochs keep counting across calls (stored in the
+// header), so no barrier is needed between calls.  A wait that exceeds ~4 s raises `error` and ends
+// the kernel instead of hanging the GPU.
+constexpr int kXchgMaxRanks = 16;
+constexpr int kXchgSliceWordsCap = kMaxChunks * kChunkWords;  // words per parity buffer (all ranks together)
+
+struct XchgHeader {            // at the start of every rank's exchange buffer
+    unsigned int epoch;        // last epoch this rank completed (persists across calls)
+    unsigned int error;        // 1 = a wait timed out
+    unsigned int pad0[62];
+    unsigned int flags[64];    // flags[q] = last epoch whose slice sender q has delivered here
+    unsigned int pad1[64];
+};
+static_assert(sizeof(XchgHeader) == 768, "header layout");
+
+__host__ __device__ inline size_t xchg_buffer_bytes() {
+    return sizeof(XchgHeader) + sizeof(uint32_t) * 2 * (size_t)kXchgSliceWordsCap;
+}
+__device__ __forceinline__ uint32_t *xchg_slices(unsigned char *base, int parity) {
+    return reinterpret_cast<uint32_t *>(base + sizeof(XchgHeader)) + (size_t)parity * kXchgSliceWordsCap;
+}
+
+struct XchgCtx {
+    unsigned char *const *peers;  // device array: peers[q] = rank q's exchange buffer (peers[me] is local)
+    int me, nranks, slice_chunks;
+};
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+template <int kPer>
+__global__ void __launch_bounds__(kPeelThreads)
+peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, ChunkMap cm,
+                int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm, int *__restrict__ list,
+                int *__restrict__ cnt, uint32_t *__restrict__ mybits, XchgCtx x, int *__restrict__ fronts_done) {
+    __shared__ PeelSmem sm;
+    __shared__ PrefixSmem ps;
+    __shared__ int sh_wsum[kPeelThreads / 32];
+    __shared__ int sh_fail;
+    cg::grid_group grid = cg::this_grid();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char *self = x.peers[x.me];
+    XchgHeader *hdr = reinterpret_cast<XchgHeader *>(self);
+    unsigned int e = *reinterpret_cast<volatile unsigned int *>(&hdr->epoch);
+    const int slice_words = x.slice_chunks * kChunkWords;
+    int r = 0;
+    bool failed = false;
+    for (;;) {
+        ++e;
+        // 1. front among my own columns -> mybits (zero padding beyond my local chunks stays zero)
+        {
+            const int64_t words = (int64_t)cm.nlocal * kChunkWords;
+            const int64_t nwarps = (int64_t)gridDim.x * (kPeelThreads / 32);
+            for (int64_t gw = (int64_t)blockIdx.x * (kPeelThreads / 32) + warp; gw < words; gw += nwarps) {
+                const int lc = (int)(gw / kChunkWords);
+                const int64_t j = (int64_t)cm.global(lc) * kChunkCols + (gw % kChunkWords) * 32 + lane;
+                const bool in = (j < n) && (__ldcg(count + j) == 0);
+                if (in) count[j] = -1;
+                const uint32_t m = __ballot_sync(0xffffffffu, in);
+                if (lane == 0) mybits[gw] = m;
+            }
+        }
+        grid.sync();
+        // 2. block 0 delivers my slice to every rank (my own buffer included) and raises the flags
+        if (blockIdx.x == 0) {
+            for (int q = 0; q < x.nranks; ++q) {
+                uint32_t *dst = xchg_slices(x.peers[q], e & 1) + (size_t)x.me * slice_words;
+                for (int w = threadIdx.x; w < slice_words; w += kPeelThreads) dst[w] = __ldcg(mybits + w);
+            }
+            __threadfence_system();
+            __syncthreads();
+            if (threadIdx.x < x.nranks) {
+                XchgHeader *ph = reinterpret_cast<XchgHeader *>(x.peers[threadIdx.x]);
+                *reinterpret_cast<volatile unsigned int *>(&ph->flags[x.me]) = e;
+            }
+        }
+        // 3. every CTA waits until all senders' slices of this epoch are here
+        if (threadIdx.x == 0) sh_fail = 0;
+        __syncthreads();
+        if (threadIdx.x < x.nranks) {
+            const volatile unsigned int *f = &hdr->flags[threadIdx.x];
+            const unsigned long long t0 = global_ns();
+            while ((int)(*f - e) < 0) {
+                if (global_ns() - t0 > 4000000000ull || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
+                    sh_fail = 1;
+                    break;
+                }
+            }
+        }
+        __syncthreads();
+        if (sh_fail) {
+            if (threadIdx.x == 0) hdr->error = 1;
+            failed = true;
+            break;
+        }
+        __threadfence_system();
+        // 4. bitmask of all ranks -> region-major member lists, ranks, region sizes
+        {
+            const uint32_t *gathered = xchg_slices(self, e & 1);
+            for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+                const int owner = c % x.nranks, lc = c / x.nranks;
+                uint32_t w = 0u;
+                if (threadIdx.x < kChunkWords)
+                    w = __ldcg(gathered + ((size_t)owner * x.slice_chunks + lc) * kChunkWords + threadIdx.x);
+                const int mine = __popc(w);
+                int incl = mine;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += t;
+                }
+                __syncthreads();
+                if (lane == 31) sh_wsum[warp] = incl;
+                __syncthreads();
+                int before = incl - mine;
+                for (int q = 0; q < warp; ++q) before += sh_wsum[q];
+                int pos = before;
+                while (w) {
+                    const int b = __ffs(w) - 1;
+                    w &= w - 1;
+                    const int j = c * kChunkCols + threadIdx.x * 32 + b;
+                    list[(int64_t)c * kChunkCols + pos++] = j;
+                    rank[perm ? perm[j] : j] = r;
+                }
+                if (threadIdx.x == kPeelThreads - 1) cnt[c] = before + mine;
+            }
+        }
+        grid.sync();
+        // 5. subtract the front's rows from my columns
+        build_prefix_t<kPer>(cnt, nchunks, n, true, cm, ps);
+        if (ps.pc[nchunks] == 0) break;  // the same bitmask everywhere: every rank stops at the same front
+        accumulate_front(D, row_words, nchunks, true, cm, list, ps, count, -1, sm);
+        grid.sync();
+        ++r;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (!failed) hdr->epoch = e;
+        *fronts_done = failed ? -1 : r;
+    }
+}
+
 }  // namespace evoxb

@@ -104,6 +104,14 @@ class ShardedSelector:
             _lib.check(L.evoxb_nds_sharded_workspace_bytes(n, m, self.rank, self.nranks, ctypes.byref(need)))
             self._ws = torch.empty(need.value, dtype=torch.uint8, device=self.device)
 
+    def status(self):
+        """(peer_memory_path, error, fronts_of_last_call) -- synchronises the device."""
+        a, b, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        torch.cuda.synchronize(self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().evoxb_comm_status(self._comm, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return bool(a.value), bool(b.value), c.value
+
     def close(self):
         if getattr(self, "_comm", None):
             _lib.lib().evoxb_comm_destroy(self._comm)

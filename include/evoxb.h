@@ -139,6 +139,11 @@ typedef struct evoxb_comm evoxb_comm_t;
 EVOXB_API int evoxb_comm_unique_id(void *id128);
 EVOXB_API int evoxb_comm_create(const void *id128, int rank, int nranks, evoxb_comm_t **out);
 EVOXB_API int evoxb_comm_destroy(evoxb_comm_t *comm);
+/* p2p_enabled: 1 when the ranks exchange the front bitmask through peer memory inside one persistent
+ * kernel (CUDA IPC + NVLink; the default when every rank can map every peer), 0 when they fall back
+ * to one ncclAllGather per front.  error: 1 if a peer did not answer within ~4 s during the last
+ * call.  fronts: number of fronts of the last peer-memory call.  Synchronous (small D2H copies).    */
+EVOXB_API int evoxb_comm_status(evoxb_comm_t *comm, int *p2p_enabled, int *error, int *fronts);
 EVOXB_API int evoxb_shard_plan(int64_t n, int rank, int nranks, int *first_chunk, int *chunk_stride,
                                int *local_chunks, int *total_chunks);
 EVOXB_API int evoxb_nds_sharded_workspace_bytes(int64_t n, int m, int rank, int nranks, size_t *bytes);

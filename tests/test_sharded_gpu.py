@@ -24,7 +24,9 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, cases, out):
+def _worker(rank, world, port, cases, out, no_p2p=False):
+    if no_p2p:
+        os.environ["EVOXB_NO_P2P"] = "1"
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch
@@ -52,6 +54,8 @@ def _worker(rank, world, port, cases, out):
         ok = (np.array_equal(r1, w_rank) and np.array_equal(r2, w_rank) and np.array_equal(rk, w_rank)
               and np.array_equal(order, w_order) and np.array_equal(np.isfinite(crowd), fin)
               and np.allclose(crowd[fin], w_crowd[fin], rtol=1e-6, atol=0))
+        p2p, err, fronts = sel.status()
+        ok = ok and not err and (p2p != no_p2p) and (not p2p or fronts == int(w_rank.max()) + 1)
         res.append((kind, n, m, bool(ok)))
         sel.close()
     out[rank] = res
@@ -62,24 +66,26 @@ CASES = [("uniform", 5000, 3, 1), ("nasty", 9001, 4, 2), ("uniform", 20000, 2, 3
          ("uniform", 40000, 5, 5)]
 
 
-def _run(world):
+def _run(world, no_p2p=False):
     import torch.multiprocessing as mp
 
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_worker, args=(world, _free_port(), CASES, out), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), CASES, out, no_p2p), nprocs=world, join=True)
     assert len(out) == world
     for r in range(world):
         for kind, n, m, ok in out[r]:
             assert ok, f"rank {r} of {world}: {kind} {n}x{m} differs from the oracle"
 
 
-def test_sharded_world_size_1():
-    _run(1)
+@pytest.mark.parametrize("no_p2p", [False, True], ids=["peer_memory", "nccl_allgather"])
+def test_sharded_world_size_1(no_p2p):
+    _run(1, no_p2p)
 
 
+@pytest.mark.parametrize("no_p2p", [False, True], ids=["peer_memory", "nccl_allgather"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_sharded_multi_gpu(world):
+def test_sharded_multi_gpu(world, no_p2p):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    _run(world)
+    _run(world, no_p2p)
