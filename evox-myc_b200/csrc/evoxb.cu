@@ -124,25 +124,26 @@ static int check_common(const void *fitness, int64_t n, int m) {
     return 0;
 }
 
-static int peel_grid(int *blocks) {
-    static thread_local int cached_dev = -1, cached_blocks = 0;
+// Largest co-resident grid (capped at `cap_per_sm` CTAs per SM) for a cooperative kernel, cached per
+// (device, kernel).  Every template instance has its own register count, so each is queried itself.
+static int coop_blocks(const void *kern, int threads, int cap_per_sm, int *blocks) {
+    struct Entry { int dev; const void *kern; int blocks; };
+    static thread_local Entry cache[16];
+    static thread_local int used = 0;
     int dev = 0;
     EVOXB_CUDA(cudaGetDevice(&dev));
-    if (dev != cached_dev) {
-        int sms = 0, per_sm = 0;
-        EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peel_persistent_kernel<kMaxChunks / 32>,
-                                                                 kPeelThreads, 0));
-        int per_sm_p2p = 0;
-        EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_p2p, peel_p2p_kernel<kMaxChunks / 32>,
-                                                                 kPeelThreads, 0));
-        if (per_sm_p2p < per_sm) per_sm = per_sm_p2p;  // one grid size serves both cooperative kernels
-        if (per_sm < 1) return fail(EVOXB_E_CUDA, "peel kernel does not fit on an SM");
-        if (per_sm > 3) per_sm = 3;
-        cached_blocks = sms * per_sm;
-        cached_dev = dev;
-    }
-    *blocks = cached_blocks;
+    for (int i = 0; i < used; ++i)
+        if (cache[i].dev == dev && cache[i].kern == kern) {
+            *blocks = cache[i].blocks;
+            return 0;
+        }
+    int sms = 0, per_sm = 0;
+    EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessorWithFlags(&per_sm, kern, threads, 0, cudaOccupancyDefault));
+    if (per_sm < 1) return fail(EVOXB_E_CUDA, "a cooperative kernel does not fit on an SM");
+    if (per_sm > cap_per_sm) per_sm = cap_per_sm;
+    *blocks = sms * per_sm;
+    if (used < 16) cache[used++] = Entry{dev, kern, *blocks};
     return 0;
 }
 
@@ -153,23 +154,6 @@ namespace evoxb {
 
 // Presort by (key_0, S') + sorted objective-major copy + uids (presort.cuh).  Deterministic, so
 // every GPU of a sharded run computes the same permutation on its own.
-static int presort_grid(int *blocks) {
-    static thread_local int cached_dev = -1, cached_blocks = 0;
-    int dev = 0;
-    EVOXB_CUDA(cudaGetDevice(&dev));
-    if (dev != cached_dev) {
-        int sms = 0, per_sm = 0;
-        EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, presort_coop_kernel, 256, 0));
-        if (per_sm < 1) return fail(EVOXB_E_CUDA, "presort kernel does not fit on an SM");
-        if (per_sm > 2) per_sm = 2;
-        cached_blocks = sms * per_sm;
-        cached_dev = dev;
-    }
-    *blocks = cached_blocks;
-    return 0;
-}
-
 static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &L, cudaStream_t s) {
     // order by (key_0, S'): stable LSD passes over S' (low 32 bits, then the few high bits), then key_0
     PresortPasses pp{};
@@ -179,7 +163,7 @@ static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &
     }
     for (int sh = 0; sh < 32; sh += 8) { pp.kind[pp.count] = 2; pp.shift[pp.count++] = sh; }
     int blocks = 0;
-    if (int rc = presort_grid(&blocks)) return rc;
+    if (int rc = coop_blocks((const void *)presort_coop_kernel, 256, 2, &blocks)) return rc;
     const int tiles = (int)div_up(L.npad, kCoopTile);
     if (blocks > tiles) blocks = tiles;
     const float *x = fitness;
@@ -214,8 +198,12 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         if (int rc = launch_dominance_build(L.xt, L.npad, 0, n, m, L.D, L.row_words, s)) return rc;
     }
 
+    // entries per lane of the region-prefix scan: 1 up to 32 chunks (N <= 131072), 4 up to 128, else 16
+    const void *peel_kern = L.nchunks <= 32    ? (const void *)peel_persistent_kernel<1>
+                            : L.nchunks <= 128 ? (const void *)peel_persistent_kernel<4>
+                                               : (const void *)peel_persistent_kernel<kMaxChunks / 32>;
     int blocks = 0;
-    if (int rc = peel_grid(&blocks)) return rc;
+    if (int rc = coop_blocks(peel_kern, kPeelThreads, 3, &blocks)) return rc;
     const int tri = L.tri ? 1 : 0;
 
     prof.mark("dominator_count", s);
@@ -235,11 +223,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         int *list = L.list;
         PeelCtrl *ctrl = L.ctrl;
         void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl};
-        // entries per lane of the region-prefix scan: 1 up to 32 chunks (N <= 131072), 4 up to 128, else 16
-        const void *kern = L.nchunks <= 32    ? (const void *)peel_persistent_kernel<1>
-                           : L.nchunks <= 128 ? (const void *)peel_persistent_kernel<4>
-                                              : (const void *)peel_persistent_kernel<kMaxChunks / 32>;
-        EVOXB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
+        EVOXB_CUDA(cudaLaunchCooperativeKernel(peel_kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
     }
     return 0;
@@ -303,8 +287,11 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
     prof.mark("dominance_build", s);
     if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.D, L.row_words, s, &L.cm)) return rc;
 
+    const void *p2p_kern = L.nchunks <= 32    ? (const void *)peel_p2p_kernel<1>
+                           : L.nchunks <= 128 ? (const void *)peel_p2p_kernel<4>
+                                              : (const void *)peel_p2p_kernel<kMaxChunks / 32>;
     int blocks = 0;
-    if (int rc = peel_grid(&blocks)) return rc;
+    if (int rc = coop_blocks(p2p_kern, kPeelThreads, 3, &blocks)) return rc;
     prof.mark("dominator_count", s);
     if (L.cm.nlocal > 0) {
         dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, 1, L.cm, L.count);
@@ -325,10 +312,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         uint32_t *mybits = L.send_bits;
         XchgCtx x{comm->peers_dev, comm->rank, comm->nranks, L.slice_chunks};
         void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &mybits, &x, &fronts};
-        const void *kern = L.nchunks <= 32    ? (const void *)peel_p2p_kernel<1>
-                           : L.nchunks <= 128 ? (const void *)peel_p2p_kernel<4>
-                                              : (const void *)peel_p2p_kernel<kMaxChunks / 32>;
-        EVOXB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
+        EVOXB_CUDA(cudaLaunchCooperativeKernel(p2p_kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
         return 0;
     }

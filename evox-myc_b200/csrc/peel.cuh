@@ -451,14 +451,15 @@ front_subtract_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nch
 
 // ---- multi-GPU, fused: the front loop and its exchange in ONE persistent kernel per GPU ---------------
 // Instead of three launches and an ncclAllGather per front, every GPU runs one cooperative kernel for
-// the whole peel.  Per front it marks the front among its own columns, block 0 stores that slice of
-// the bitmask straight into every peer's exchange buffer over NVLink (peer pointers obtained through
-// CUDA IPC at communicator creation), raises a per-sender epoch flag on each peer, and all CTAs wait
-// for the flags of all senders in local memory.  The exchange buffer is double-buffered by epoch
-// parity: a sender can be at most one front ahead of the slowest reader, because it needs that
-// reader's slice of the next front to go further.  Epochs keep counting across calls (stored in the
-// header), so no barrier is needed between calls.  A wait that exceeds ~4 s raises `error` and ends
-// the kernel instead of hanging the GPU.
+// the whole peel.  Per front it marks the front among its own columns and CTA q stores that slice of
+// the bitmask straight into rank q's exchange buffer over NVLink (peer pointers obtained through
+// CUDA IPC at communicator creation).  Every 32-bit word of the bitmask travels as one 8-byte store
+// {word, epoch}: 8-byte stores arrive whole, so the reader spins on the epoch tag of exactly the word
+// it needs and no fence, flag or separate wait phase is required (the low-latency protocol NCCL uses
+// for small messages).  The buffer is double-buffered by epoch parity: a sender can be at most one
+// front ahead of the slowest reader, because it needs that reader's slice of the next front to go
+// further.  Epochs keep counting across calls (stored in the header), so no barrier is needed
+// between calls.  A wait that exceeds ~4 s raises `error` and ends the kernel instead of hanging the GPU.
 constexpr int kXchgMaxRanks = 16;
 constexpr int kXchgSliceWordsCap = kMaxChunks * kChunkWords;  // words per parity buffer (all ranks together)
 
@@ -472,16 +473,26 @@ struct XchgHeader {            // at the start of every rank's exchange buffer
 static_assert(sizeof(XchgHeader) == 768, "header layout");
 
 __host__ __device__ inline size_t xchg_buffer_bytes() {
-    return sizeof(XchgHeader) + sizeof(uint32_t) * 2 * (size_t)kXchgSliceWordsCap;
+    return sizeof(XchgHeader) + sizeof(uint2) * 2 * (size_t)kXchgSliceWordsCap;
 }
-__device__ __forceinline__ uint32_t *xchg_slices(unsigned char *base, int parity) {
-    return reinterpret_cast<uint32_t *>(base + sizeof(XchgHeader)) + (size_t)parity * kXchgSliceWordsCap;
+__device__ __forceinline__ uint2 *xchg_slices(unsigned char *base, int parity) {
+    return reinterpret_cast<uint2 *>(base + sizeof(XchgHeader)) + (size_t)parity * kXchgSliceWordsCap;
 }
 
 struct XchgCtx {
     unsigned char *const *peers;  // device array: peers[q] = rank q's exchange buffer (peers[me] is local)
     int me, nranks, slice_chunks;
 };
+
+// single 8-byte transactions (never torn): the {word, epoch} pairs of the exchange protocol
+__device__ __forceinline__ uint2 ld_volatile_u2(const uint2 *p) {
+    uint2 v;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u2(uint2 *p, uint2 v) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
 
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
@@ -522,47 +533,40 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
             }
         }
         grid.sync();
-        // 2. block 0 delivers my slice to every rank (my own buffer included) and raises the flags
-        if (blockIdx.x == 0) {
-            for (int q = 0; q < x.nranks; ++q) {
-                uint32_t *dst = xchg_slices(x.peers[q], e & 1) + (size_t)x.me * slice_words;
-                for (int w = threadIdx.x; w < slice_words; w += kPeelThreads) dst[w] = __ldcg(mybits + w);
-            }
-            __threadfence_system();
-            __syncthreads();
-            if (threadIdx.x < x.nranks) {
-                XchgHeader *ph = reinterpret_cast<XchgHeader *>(x.peers[threadIdx.x]);
-                *reinterpret_cast<volatile unsigned int *>(&ph->flags[x.me]) = e;
-            }
+        // 2. CTA q (< nranks) delivers my slice to rank q (my own buffer included): one 8-byte
+        //    {word, epoch} store per bitmask word, no fence
+        for (int q = blockIdx.x; q < x.nranks; q += gridDim.x) {
+            uint2 *dst = xchg_slices(x.peers[q], e & 1) + (size_t)x.me * slice_words;
+            for (int w = threadIdx.x; w < slice_words; w += kPeelThreads)
+                st_volatile_u2(dst + w, make_uint2(__ldcg(mybits + w), e));
         }
-        // 3. every CTA waits until all senders' slices of this epoch are here
+        // 3+4. bitmask of all ranks -> region-major member lists, ranks, region sizes; a reader spins on
+        //      the epoch tag of the word it needs
         if (threadIdx.x == 0) sh_fail = 0;
         __syncthreads();
-        if (threadIdx.x < x.nranks) {
-            const volatile unsigned int *f = &hdr->flags[threadIdx.x];
-            const unsigned long long t0 = global_ns();
-            while ((int)(*f - e) < 0) {
-                if (global_ns() - t0 > 4000000000ull || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
-                    sh_fail = 1;
-                    break;
-                }
-            }
-        }
-        __syncthreads();
-        if (sh_fail) {
-            if (threadIdx.x == 0) hdr->error = 1;
-            failed = true;
-            break;
-        }
-        __threadfence_system();
-        // 4. bitmask of all ranks -> region-major member lists, ranks, region sizes
         {
-            const uint32_t *gathered = xchg_slices(self, e & 1);
+            const uint2 *gathered = xchg_slices(self, e & 1);
             for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
                 const int owner = c % x.nranks, lc = c / x.nranks;
                 uint32_t w = 0u;
-                if (threadIdx.x < kChunkWords)
-                    w = __ldcg(gathered + ((size_t)owner * x.slice_chunks + lc) * kChunkWords + threadIdx.x);
+                if (threadIdx.x < kChunkWords) {
+                    const uint2 *src = gathered + ((size_t)owner * x.slice_chunks + lc) * kChunkWords + threadIdx.x;
+                    uint2 v = ld_volatile_u2(src);
+                    unsigned long long t0 = 0ull;
+                    unsigned int spins = 0u;
+                    while (v.y != e) {
+                        if ((++spins & 1023u) == 0u) {
+                            const unsigned long long now = global_ns();
+                            if (t0 == 0ull) t0 = now;
+                            if (now - t0 > 4000000000ull || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
+                                sh_fail = 1;
+                                break;
+                            }
+                        }
+                        v = ld_volatile_u2(src);
+                    }
+                    w = v.x;
+                }
                 const int mine = __popc(w);
                 int incl = mine;
 #pragma unroll
@@ -573,6 +577,7 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
                 __syncthreads();
                 if (lane == 31) sh_wsum[warp] = incl;
                 __syncthreads();
+                if (sh_fail) break;
                 int before = incl - mine;
                 for (int q = 0; q < warp; ++q) before += sh_wsum[q];
                 int pos = before;
@@ -586,7 +591,15 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
                 if (threadIdx.x == kPeelThreads - 1) cnt[c] = before + mine;
             }
         }
+        if (sh_fail) {  // a peer never delivered: flag it (all CTAs see hdr->error and leave too)
+            if (threadIdx.x == 0) hdr->error = 1;
+            failed = true;
+        }
         grid.sync();
+        if (*reinterpret_cast<volatile unsigned int *>(&hdr->error)) {  // uniform across the grid after the sync
+            failed = true;
+            break;
+        }
         // 5. subtract the front's rows from my columns
         build_prefix_t<kPer>(cnt, nchunks, n, true, cm, ps);
         if (ps.pc[nchunks] == 0) break;  // the same bitmask everywhere: every rank stops at the same front
