@@ -458,8 +458,10 @@ front_subtract_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nch
 // it needs and no fence, flag or separate wait phase is required (the low-latency protocol NCCL uses
 // for small messages).  The buffer is double-buffered by epoch parity: a sender can be at most one
 // front ahead of the slowest reader, because it needs that reader's slice of the next front to go
-// further.  Epochs keep counting across calls (stored in the header), so no barrier is needed
-// between calls.  A wait that exceeds ~4 s raises `error` and ends the kernel instead of hanging the GPU.
+// further -- every rank waits for a per-sender heartbeat of the epoch even when it needs none of that
+// sender's words (a rank that owns no chunk would otherwise let the others run ahead and overwrite
+// words it has not read yet).  Epochs keep counting across calls (stored in the header), so no barrier
+// is needed between calls.  A wait that exceeds ~4 s raises `error` and ends the kernel instead of hanging the GPU.
 constexpr int kXchgMaxRanks = 16;
 constexpr int kXchgSliceWordsCap = kMaxChunks * kChunkWords;  // words per parity buffer (all ranks together)
 
@@ -467,10 +469,11 @@ struct XchgHeader {            // at the start of every rank's exchange buffer
     unsigned int epoch;        // last epoch this rank completed (persists across calls)
     unsigned int error;        // 1 = a wait timed out
     unsigned int pad0[62];
-    unsigned int flags[64];    // flags[q] = last epoch whose slice sender q has delivered here
-    unsigned int pad1[64];
+    unsigned int flags[64];    // (unused by the tagged protocol)
+    uint2 hb[2][16];           // hb[parity][q] = {0, epoch}: sender q has started delivering that epoch
 };
 static_assert(sizeof(XchgHeader) == 768, "header layout");
+static_assert(kXchgMaxRanks <= 16, "hb[] holds 16 senders");
 
 __host__ __device__ inline size_t xchg_buffer_bytes() {
     return sizeof(XchgHeader) + sizeof(uint2) * 2 * (size_t)kXchgSliceWordsCap;
@@ -539,11 +542,30 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
             uint2 *dst = xchg_slices(x.peers[q], e & 1) + (size_t)x.me * slice_words;
             for (int w = threadIdx.x; w < slice_words; w += kPeelThreads)
                 st_volatile_u2(dst + w, make_uint2(__ldcg(mybits + w), e));
+            if (threadIdx.x == 0)
+                st_volatile_u2(&reinterpret_cast<XchgHeader *>(x.peers[q])->hb[e & 1][x.me], make_uint2(0u, e));
         }
         // 3+4. bitmask of all ranks -> region-major member lists, ranks, region sizes; a reader spins on
         //      the epoch tag of the word it needs
         if (threadIdx.x == 0) sh_fail = 0;
         __syncthreads();
+        if (blockIdx.x == 0 && threadIdx.x < x.nranks) {  // heartbeats of all senders (see the header comment)
+            const uint2 *src = &hdr->hb[e & 1][threadIdx.x];
+            uint2 v = ld_volatile_u2(src);
+            unsigned long long t0 = 0ull;
+            unsigned int spins = 0u;
+            while (v.y != e) {
+                if ((++spins & 1023u) == 0u) {
+                    const unsigned long long now = global_ns();
+                    if (t0 == 0ull) t0 = now;
+                    if (now - t0 > 4000000000ull || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
+                        sh_fail = 1;
+                        break;
+                    }
+                }
+                v = ld_volatile_u2(src);
+            }
+        }
         {
             const uint2 *gathered = xchg_slices(self, e & 1);
             for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {

@@ -51,12 +51,18 @@ def _worker(rank, world, port, cases, out, no_p2p=False):
         order, rk, crowd = sel.nsga2_select(x, pop, return_details=True)
         w_order, w_rank, w_crowd = c_oracle.nsga2_select(x, pop)
         fin = np.isfinite(w_crowd)
-        ok = (np.array_equal(r1, w_rank) and np.array_equal(r2, w_rank) and np.array_equal(rk, w_rank)
-              and np.array_equal(order, w_order) and np.array_equal(np.isfinite(crowd), fin)
-              and np.allclose(crowd[fin], w_crowd[fin], rtol=1e-6, atol=0))
         p2p, err, fronts = sel.status()
-        ok = ok and not err and (p2p != no_p2p) and (not p2p or fronts == int(w_rank.max()) + 1)
-        res.append((kind, n, m, bool(ok)))
+        why = []
+        if not np.array_equal(r1, w_rank): why.append(f"ranks differ in {int(np.sum(r1 != w_rank))} rows (host input)")
+        if not np.array_equal(r2, w_rank): why.append(f"ranks differ in {int(np.sum(r2 != w_rank))} rows (device input)")
+        if not np.array_equal(rk, w_rank): why.append("select: ranks differ")
+        if not np.array_equal(order, w_order): why.append("select: survivor order differs")
+        if not (np.array_equal(np.isfinite(crowd), fin) and np.allclose(crowd[fin], w_crowd[fin], rtol=1e-6, atol=0)):
+            why.append("select: crowding differs")
+        if err: why.append("a peer timed out")
+        if p2p == no_p2p: why.append(f"peer-memory path enabled={p2p}, expected {not no_p2p}")
+        if p2p and fronts != int(w_rank.max()) + 1: why.append(f"fronts {fronts} != {int(w_rank.max()) + 1}")
+        res.append((kind, n, m, "; ".join(why)))
         sel.close()
     out[rank] = res
     dist.destroy_process_group()
@@ -74,8 +80,8 @@ def _run(world, no_p2p=False):
     mp.spawn(_worker, args=(world, _free_port(), CASES, out, no_p2p), nprocs=world, join=True)
     assert len(out) == world
     for r in range(world):
-        for kind, n, m, ok in out[r]:
-            assert ok, f"rank {r} of {world}: {kind} {n}x{m} differs from the oracle"
+        for kind, n, m, why in out[r]:
+            assert not why, f"rank {r} of {world}: {kind} {n}x{m}: {why}"
 
 
 @pytest.mark.parametrize("no_p2p", [False, True], ids=["peer_memory", "nccl_allgather"])
