@@ -30,6 +30,8 @@ EXPORTS = [
     "evoxb_argsort_workspace_bytes",
     "evoxb_argsort_f32",
     "evoxb_gather_rows_f32",
+    "evoxb_sbx_pm_clip_f32",
+    "evoxb_dtlz2_f32",
     "evoxb_comm_unique_id",
     "evoxb_comm_create",
     "evoxb_comm_destroy",
@@ -74,6 +76,9 @@ def lib() -> ctypes.CDLL:
         L.evoxb_argsort_workspace_bytes.argtypes = [i64, ctypes.POINTER(sz)]
         L.evoxb_argsort_f32.argtypes = [vp, i64, vp, vp, sz, vp]
         L.evoxb_gather_rows_f32.argtypes = [vp, i64, i64, vp, i64, vp, vp]
+        f32, u32 = ctypes.c_float, ctypes.c_uint32
+        L.evoxb_sbx_pm_clip_f32.argtypes = [vp, i64, i32, vp, vp, f32, f32, f32, f32, u32, u32, vp, vp]
+        L.evoxb_dtlz2_f32.argtypes = [vp, i64, i32, i32, vp, vp]
         ip = ctypes.POINTER(ctypes.c_int)
         L.evoxb_comm_unique_id.argtypes = [vp]
         L.evoxb_comm_create.argtypes = [ctypes.c_char_p, i32, i32, ctypes.POINTER(vp)]

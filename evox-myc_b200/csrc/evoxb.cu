@@ -14,6 +14,7 @@
 #include "presort.cuh"
 #include "crowding.cuh"
 #include "select.cuh"
+#include "variation.cuh"
 
 namespace evoxb {
 
@@ -755,6 +756,30 @@ EVOXB_API int evoxb_nsga2_select_sharded_f32(const float *fitness, int64_t n, in
                                    evoxb_stream_t stream) {
     if (!comm) return fail(EVOXB_E_INVALID, "comm is null");
     return select_impl(0, fitness, n, m, pop_size, order, rank_out, crowd_out, ws, ws_bytes, stream, comm);
+}
+
+EVOXB_API int evoxb_sbx_pm_clip_f32(const float *pop, int64_t n, int d, const float *lb, const float *ub, float pro_c,
+                          float dis_c, float pro_m, float dis_m, uint32_t seed, uint32_t generation, float *out,
+                          evoxb_stream_t stream) {
+    if (n < 0 || d < 1) return fail(EVOXB_E_INVALID, "bad shape (%lld, %d)", (long long)n, d);
+    if (n == 0) return 0;
+    if (!pop || !lb || !ub || !out) return fail(EVOXB_E_INVALID, "null pointer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int64_t work = (n / 2) * d + ((n & 1) ? d : 0);
+    sbx_pm_clip_kernel<<<(unsigned)div_up(work > 0 ? work : 1, 256), 256, 0, s>>>(pop, n, d, lb, ub, pro_c, dis_c, pro_m,
+                                                                                dis_m, seed, generation, out);
+    EVOXB_LAUNCH_CHECK("sbx_pm_clip_kernel");
+    return 0;
+}
+
+EVOXB_API int evoxb_dtlz2_f32(const float *x, int64_t n, int d, int m, float *f, evoxb_stream_t stream) {
+    if (n < 0 || m < 1 || d < m) return fail(EVOXB_E_INVALID, "bad shape (n=%lld, d=%d, m=%d)", (long long)n, d, m);
+    if (n == 0) return 0;
+    if (!x || !f) return fail(EVOXB_E_INVALID, "null pointer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    dtlz2_kernel<<<(unsigned)div_up(n, 128), 128, 0, s>>>(x, n, d, m, f);
+    EVOXB_LAUNCH_CHECK("dtlz2_kernel");
+    return 0;
 }
 
 EVOXB_API int evoxb_argsort_workspace_bytes(int64_t n, size_t *bytes) {

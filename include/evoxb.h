@@ -124,6 +124,18 @@ EVOXB_API int evoxb_argsort_f32(const float *x, int64_t n, int32_t *idx, void *w
 EVOXB_API int evoxb_gather_rows_f32(const float *src, int64_t n, int64_t d, const int32_t *idx, int64_t k,
                                     float *dst, evoxb_stream_t stream);
 
+/* ---- next row 2: what NSGA-II does between two selections -----------------------------------------
+ * evoxb_sbx_pm_clip_f32 = NSGA2.ask (src/evox/algorithms/mo/nsga2.py:76-84): simulated binary
+ * crossover of rows [0, n/2) with rows [n/2, 2*(n/2)) (operators/crossover/sbx.py:8-41, type 1),
+ * polynomial mutation (operators/mutation/pm_mutation.py:6-54) and clip to [lb, ub].  pop, out are
+ * (n, d); lb, ub are (d).  Random numbers are Philox-4x32-10 keyed by (seed, generation): the same
+ * arguments give the same offspring; JAX's threefry streams are not reproduced (statistical parity).
+ * evoxb_dtlz2_f32 = DTLZ2.evaluate (src/evox/problems/numerical/dtlz.py:84-103): x (n, d) -> f (n, m). */
+EVOXB_API int evoxb_sbx_pm_clip_f32(const float *pop, int64_t n, int d, const float *lb, const float *ub,
+                                    float pro_c, float dis_c, float pro_m, float dis_m, uint32_t seed,
+                                    uint32_t generation, float *out, evoxb_stream_t stream);
+EVOXB_API int evoxb_dtlz2_f32(const float *x, int64_t n, int d, int m, float *f, evoxb_stream_t stream);
+
 /* ---- e: multi-GPU ranking, one process per GPU (no counterpart in the reference, whose tell() is
  * replicated on every device: src/evox/workflows/std_workflow.py:194, :341) ---------------------------
  * The bit-packed dominance matrix is sharded by COLUMN chunk (4096 dominated individuals per chunk,
