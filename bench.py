@@ -308,6 +308,10 @@ def run_gpu_arm(args, n, m, desc):
                       "executed": exe_ops / 1e12, "executed_frac": exe_ops / peak_ops,
                       "ms_per_launch": build_ms, "pairs_per_s": pairs_rank / (build_ms * 1e-3)})
 
+    nsga2_info = None
+    if world == 1 and not args.no_nsga2:
+        nsga2_info = bench_nsga2(args, dev)
+
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         from oracle import c_oracle
@@ -335,10 +339,68 @@ def run_gpu_arm(args, n, m, desc):
         "kernels": extra,
         "stages_ms": {k: round(v, 4) for k, v in stages.items()},
         "cpu_baseline": cpu,
+        "nsga2": nsga2_info,
     }
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def bench_nsga2(args, dev):
+    """The other half of BASELINE.json's metric: NSGA-II generations/s.
+
+    GPU: BASELINE configs[2] -- DTLZ2, pop = 16384, M = 3, D = 12; one generation = ask (SBX + polynomial
+    mutation + clip) + evaluate + tell (ranking, crowding, survivor gather), all native kernels.
+    CPU: BASELINE configs[0] shape -- pop = 100, 100 generations -- with the NumPy restatement
+    (oracle/), one core; trajectories are not comparable with JAX's (different PRNG).
+    """
+    import torch
+
+    from evox_myc_b200 import nsga2
+
+    pop, m, d = 16384, 3, 12
+    algo = nsga2.NSGA2(np.zeros(d), np.ones(d), m, pop, device=dev)
+    prob = nsga2.DTLZ2(d=d, m=m)
+    state = algo.setup(0)
+    x, state = algo.init_ask(state)
+    f, _ = prob.evaluate(None, x)
+    state = algo.init_tell(state, f)
+
+    def gen(state):
+        x, state = algo.ask(state)
+        f, _ = prob.evaluate(None, x)
+        return algo.tell(state, f)
+
+    for _ in range(5):
+        state = gen(state)
+    gens = max(args.steps, 20)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(gens):
+        state = gen(state)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / gens
+    out = {"gpu": {"config": "BASELINE configs[2]: NSGA-II on DTLZ2, pop=16384, M=3, D=12", "generations": gens,
+                   "ms_per_generation": ms, "gens_per_s": 1e3 / ms,
+                   "note": "early generations (deep fronts); ask/evaluate/tell all native kernels"}}
+    try:
+        from oracle import nds_oracle, variation_oracle as vo
+
+        P = np.random.default_rng(0).random((100, d), dtype=np.float32)
+        fP = vo.dtlz2(P, m)
+        t0 = time.perf_counter()
+        for g in range(100):
+            Q = vo.nsga2_ask(P, np.zeros(d, np.float32), np.ones(d, np.float32), 0, g)
+            fQ = vo.dtlz2(Q, m)
+            P, fP = nds_oracle.nsga2_tell(P, Q, fP, fQ, 100)
+        dt = time.perf_counter() - t0
+        out["cpu_port"] = {"config": "BASELINE configs[0] shape: NSGA-II on DTLZ2, pop=100, M=3, D=12, 100 generations",
+                           "gens_per_s": 100 / dt, "cores": 1, "kind": "port (NumPy restatement)"}
+    except Exception as ex:  # pragma: no cover
+        out["cpu_port"] = {"error": repr(ex)}
+    return out
 
 
 def main():
@@ -349,6 +411,7 @@ def main():
     ap.add_argument("--impl", default="evoxb", choices=["evoxb", "reference"])
     ap.add_argument("--workload", default="c4")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-nsga2", action="store_true", help="skip the NSGA-II generations/s measurement")
     args = ap.parse_args()
     n, m, desc = parse_workload(args.workload)
     if args.impl == "reference":
