@@ -522,28 +522,27 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
     bool failed = false;
     for (;;) {
         ++e;
-        // 1. front among my own columns -> mybits (zero padding beyond my local chunks stays zero)
+        // 1+2. front among my own columns; the warp that finds a 32-column word sends it, tagged with the
+        //      epoch, straight to every rank (my own buffer included) as one 8-byte store each -- no fence,
+        //      no staging.  Padding words of my slice (ranks owning fewer chunks) are sent as zeros.
         {
-            const int64_t words = (int64_t)cm.nlocal * kChunkWords;
+            const int64_t words = (int64_t)slice_words;
+            const int64_t own_words = (int64_t)cm.nlocal * kChunkWords;
             const int64_t nwarps = (int64_t)gridDim.x * (kPeelThreads / 32);
             for (int64_t gw = (int64_t)blockIdx.x * (kPeelThreads / 32) + warp; gw < words; gw += nwarps) {
-                const int lc = (int)(gw / kChunkWords);
-                const int64_t j = (int64_t)cm.global(lc) * kChunkCols + (gw % kChunkWords) * 32 + lane;
-                const bool in = (j < n) && (__ldcg(count + j) == 0);
-                if (in) count[j] = -1;
-                const uint32_t m = __ballot_sync(0xffffffffu, in);
-                if (lane == 0) mybits[gw] = m;
+                uint32_t m = 0u;
+                if (gw < own_words) {
+                    const int lc = (int)(gw / kChunkWords);
+                    const int64_t j = (int64_t)cm.global(lc) * kChunkCols + (gw % kChunkWords) * 32 + lane;
+                    const bool in = (j < n) && (__ldcg(count + j) == 0);
+                    if (in) count[j] = -1;
+                    m = __ballot_sync(0xffffffffu, in);
+                }
+                if (lane < x.nranks)
+                    st_volatile_u2(xchg_slices(x.peers[lane], e & 1) + (size_t)x.me * slice_words + gw, make_uint2(m, e));
             }
-        }
-        grid.sync();
-        // 2. CTA q (< nranks) delivers my slice to rank q (my own buffer included): one 8-byte
-        //    {word, epoch} store per bitmask word, no fence
-        for (int q = blockIdx.x; q < x.nranks; q += gridDim.x) {
-            uint2 *dst = xchg_slices(x.peers[q], e & 1) + (size_t)x.me * slice_words;
-            for (int w = threadIdx.x; w < slice_words; w += kPeelThreads)
-                st_volatile_u2(dst + w, make_uint2(__ldcg(mybits + w), e));
-            if (threadIdx.x == 0)
-                st_volatile_u2(&reinterpret_cast<XchgHeader *>(x.peers[q])->hb[e & 1][x.me], make_uint2(0u, e));
+            if (blockIdx.x == 0 && threadIdx.x < x.nranks)
+                st_volatile_u2(&reinterpret_cast<XchgHeader *>(x.peers[threadIdx.x])->hb[e & 1][x.me], make_uint2(0u, e));
         }
         // 3+4. bitmask of all ranks -> region-major member lists, ranks, region sizes; a reader spins on
         //      the epoch tag of the word it needs
