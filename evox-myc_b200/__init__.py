@@ -12,6 +12,7 @@ from .operators import (  # noqa: F401
     non_dominate,
     non_dominated_sort,
     nsga2_select,
+    nsga3_last_rank,
 )
 from .utils import dominate_relation  # noqa: F401
 
@@ -22,5 +23,6 @@ __all__ = [
     "non_dominate",
     "NonDominate",
     "nsga2_select",
+    "nsga3_last_rank",
     "dominate_relation",
 ]

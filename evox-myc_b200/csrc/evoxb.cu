@@ -15,6 +15,7 @@
 #include "crowding.cuh"
 #include "select.cuh"
 #include "variation.cuh"
+#include "tail.cuh"
 
 namespace evoxb {
 
@@ -55,7 +56,6 @@ struct NdsLayout {
     SortBufs sb;
     int *perm;
     int *hp;
-    uint8_t *nanrow;
     int *tile_max;
     int *uid_row;
     int *uid_col;
@@ -93,14 +93,10 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
     if (L.tri) {
         L.sb.cap = L.npad;
         L.sb.tiles = (int)div_up(L.sb.cap, kSortTile);
-        for (int b = 0; b < 2; ++b) {
-            L.sb.keys[b] = c.take<uint32_t>((size_t)L.npad);
-            L.sb.vals[b] = c.take<uint32_t>((size_t)L.npad);
-        }
+        for (int b = 0; b < 2; ++b) L.sb.vals[b] = c.take<uint32_t>((size_t)L.npad);  // permutation ping-pong
         L.sb.hist = c.take<uint32_t>((size_t)kRadix * (size_t)div_up(L.npad, kCoopTile));
         L.perm = c.take<int>((size_t)L.npad);
         L.hp = c.take<int>((size_t)L.npad);
-        L.nanrow = c.take<uint8_t>((size_t)L.npad);
         L.tile_max = c.take<int>((size_t)div_up(L.npad, kCoopTile));
         L.uid_row = c.take<int>((size_t)L.npad);
         L.uid_col = c.take<int>((size_t)L.npad);
@@ -414,6 +410,11 @@ struct SelectLayout {
     NdsLayout nds;
     CrowdLayout crowd;
     SortBufs sb;
+    // fused tail (tail.cuh)
+    int *tile_a, *tile_b, *info;
+    uint32_t *list_a, *list_b, *tbuf0, *tbuf1, *thist;
+    float *contrib;
+    int64_t tcap;
     int *hist;
     int *worst;
     uint8_t *mask;
@@ -458,6 +459,20 @@ static SelectLayout select_layout(void *ws, int64_t n, int m, int nranks = 1, in
         S.sb.vals[b] = c.take<uint32_t>((size_t)S.sb.cap);
     }
     S.sb.hist = c.take<uint32_t>(sort_hist_words(S.sb.cap, 1));
+    {
+        const size_t tiles = (size_t)div_up(n1, kCoopTile);
+        const size_t segs = (size_t)(m > 2 ? m : 2);
+        S.tcap = round_up(n1, 4);
+        S.tile_a = c.take<int>(tiles);
+        S.tile_b = c.take<int>(tiles);
+        S.info = c.take<int>(64);
+        S.list_a = c.take<uint32_t>((size_t)n1);
+        S.list_b = c.take<uint32_t>((size_t)n1);
+        S.tbuf0 = c.take<uint32_t>(segs * (size_t)S.tcap);
+        S.tbuf1 = c.take<uint32_t>(segs * (size_t)S.tcap);
+        S.thist = c.take<uint32_t>(segs * tiles * kRadix);
+        S.contrib = c.take<float>((size_t)m * (size_t)n1);
+    }
     {
         char *sub = c.take<char>(0);
         S.crowd = crowd_layout(sub, n, m);
@@ -602,6 +617,26 @@ static int select_impl(int variant, const float *fitness, int64_t n, int m, int6
         if (int rc = run_nds_sharded(fitness, n, m, rank, S.nds, comm, s, prof)) return rc;
     } else {
         if (int rc = run_nds(fitness, n, m, rank, S.nds, s, prof)) return rc;
+    }
+
+    if (variant == 0) {
+        // cut-off rank, mask, crowding and survivor order in one cooperative launch (tail.cuh)
+        prof.mark("selection_tail", s);
+        EVOXB_CUDA(cudaMemsetAsync(S.hist, 0, sizeof(int) * (size_t)n, s));
+        TailArgs ta{};
+        ta.fitness = fitness; ta.rank = rank; ta.n = (int)n; ta.m = m; ta.kth = (int)kth; ta.pop = (int)pop_size;
+        ta.order = order; ta.crowd = crowd; ta.hist = S.hist; ta.tile_a = S.tile_a; ta.tile_b = S.tile_b;
+        ta.list_a = S.list_a; ta.list_b = S.list_b; ta.buf0 = S.tbuf0; ta.buf1 = S.tbuf1; ta.hist_g = S.thist;
+        ta.contrib = S.contrib; ta.cap = S.tcap; ta.info = S.info;
+        int tb = 0;
+        if (int rc = coop_blocks((const void *)select_tail_kernel, 256, 2, &tb)) return rc;
+        const int want = (int)div_up(n, kCoopTile) * (m > 2 ? m : 2);
+        if (tb > want) tb = want < 1 ? 1 : want;
+        void *targs[] = {&ta};
+        EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)select_tail_kernel, dim3(tb), dim3(256), targs, 0, s));
+        ++g_launches;
+        prof.mark("end", s);
+        return 0;
     }
 
     prof.mark("worst_rank", s);
@@ -779,6 +814,31 @@ EVOXB_API int evoxb_dtlz2_f32(const float *x, int64_t n, int d, int m, float *f,
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     dtlz2_kernel<<<(unsigned)div_up(n, 128), 128, 0, s>>>(x, n, d, m, f);
     EVOXB_LAUNCH_CHECK("dtlz2_kernel");
+    return 0;
+}
+
+EVOXB_API int evoxb_kth_rank_workspace_bytes(int64_t n, size_t *bytes) {
+    if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
+    if (n < 0) return fail(EVOXB_E_INVALID, "n must be >= 0");
+    Carver c(nullptr);
+    c.take<int>((size_t)(n > 0 ? n : 1));
+    *bytes = c.total();
+    return 0;
+}
+
+EVOXB_API int evoxb_kth_rank_i32(const int32_t *rank, int64_t n, int64_t k, int32_t *out, void *ws, size_t ws_bytes,
+                       evoxb_stream_t stream) {
+    if (n <= 0 || k < 0 || k >= n) return fail(EVOXB_E_INVALID, "k must be in [0, n) (k = %lld, n = %lld)", (long long)k, (long long)n);
+    if (!rank || !out) return fail(EVOXB_E_INVALID, "null pointer");
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255) || ws_bytes < sizeof(int) * (size_t)n)
+        return fail(EVOXB_E_WORKSPACE, "workspace missing, misaligned or too small");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int *hist = static_cast<int *>(ws);
+    EVOXB_CUDA(cudaMemsetAsync(hist, 0, sizeof(int) * (size_t)n, s));
+    rank_hist_kernel<<<(unsigned)div_up(n, 256), 256, 0, s>>>(rank, n, hist);
+    EVOXB_LAUNCH_CHECK("rank_hist_kernel");
+    kth_rank_kernel<<<1, 1024, 0, s>>>(hist, n, k, out);
+    EVOXB_LAUNCH_CHECK("kth_rank_kernel");
     return 0;
 }
 

@@ -173,3 +173,24 @@ def nsga2_select(merged_fitness, pop_size: int, return_details: bool = False):
     if return_details:
         return (rt.give_back(order, f, "sel_o"), rt.give_back(rank, f, "sel_r"), rt.give_back(crowd, f, "sel_c"))
     return rt.give_back(order, f, "sel_o")
+
+
+def nsga3_last_rank(merged_fitness, pop_size: int):
+    """The part of ``NSGA3.tell`` that is on this path -- src/evox/algorithms/mo/nsga3.py:96-98.
+
+    ``rank = non_dominated_sort(merged_fitness); last_rank = rank[argsort(rank)[pop_size]]``.
+    Returns ``(rank, last_rank)``; ``last_rank`` is a Python int for host inputs, a 0-d tensor otherwise.
+    """
+    L = _lib.lib()
+    f = rt.Arg(merged_fitness, torch.float32, "n3_f")
+    _check_2d(f, "merged_fitness")
+    n = f.dev.shape[0]
+    rank = non_dominated_sort(f.dev)
+    out = torch.empty((1,), dtype=torch.int32, device=f.dev.device)
+    with torch.cuda.device(f.dev.device):
+        ws = _ws_call(L.evoxb_kth_rank_workspace_bytes, (n,), f.dev.device)
+        _lib.check(L.evoxb_kth_rank_i32(rank.data_ptr(), n, pop_size, out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                        rt.stream_ptr(f.dev.device)))
+    if f.kind == "cuda":
+        return rank, out[0]
+    return rt.give_back(rank, f, "n3_r"), int(out.item())

@@ -106,6 +106,13 @@ EVOXB_API int evoxb_nsga2_select_f32(const float *fitness, int64_t n, int m, int
                                      int32_t *rank_out, float *crowd_out, void *ws, size_t ws_bytes,
                                      evoxb_stream_t stream);
 
+/* ---- a8: the cut-off rank, `rank[argsort(rank)[k]]` -------------------------------------------------
+ * src/evox/algorithms/mo/nsga3.py:97-98 (k = pop_size) and nsga2.py:91-92: the value of the k-th
+ * smallest rank (0-based), from a rank histogram instead of an argsort.  out is one device int32.   */
+EVOXB_API int evoxb_kth_rank_workspace_bytes(int64_t n, size_t *bytes);
+EVOXB_API int evoxb_kth_rank_i32(const int32_t *rank, int64_t n, int64_t k, int32_t *out, void *ws,
+                                 size_t ws_bytes, evoxb_stream_t stream);
+
 /* ---- a6: operator form non_dominate(population, fitness, topk) ------------------------------------
  * src/evox/operators/selection/non_dominate.py:181-195, including its quirks: the cut-off rank is
  * rank[argsort(rank)[topk-1]] (:190) and the secondary sort key is -argsort(crowding distance)

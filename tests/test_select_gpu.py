@@ -69,3 +69,17 @@ def test_non_dominate_operator():
         assert np.array_equal(gp, wp) and np.array_equal(gf, wf)
         gp2, gf2 = e.NonDominate(k)(torch.from_numpy(pop).cuda(), torch.from_numpy(fit).cuda())
         assert gp2.is_cuda and np.array_equal(gp2.cpu().numpy(), wp) and np.array_equal(gf2.cpu().numpy(), wf)
+
+
+def test_nsga3_call_site():
+    """nsga3.py:96-98: rank and last_rank = rank[argsort(rank)[pop_size]]."""
+    import evox_myc_b200 as e
+    from oracle import nds_oracle
+
+    for seed, (n, m, pop) in enumerate([(2000, 10, 1000), (3000, 3, 1500), (500, 5, 499), (64, 2, 0)]):
+        x = h.uniform(n, m, seed)
+        want_rank, want_last = nds_oracle.nsga3_last_rank(x, pop)
+        rank, last = e.nsga3_last_rank(x, pop)
+        assert np.array_equal(rank, want_rank) and last == int(want_last)
+        r2, l2 = e.nsga3_last_rank(torch.from_numpy(x).cuda(), pop)
+        assert np.array_equal(r2.cpu().numpy(), want_rank) and int(l2) == int(want_last)
