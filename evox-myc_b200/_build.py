@@ -57,6 +57,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB_PATH
 
 
+def build_ffi() -> str:
+    """Compile csrc/xla_ffi_handlers.cc -> libevoxb_ffi.so.  Needs jaxlib's XLA FFI headers, which are
+    absent on this image (the function then raises); never called by build()."""
+    try:
+        import jax.ffi  # noqa: F401
+    except Exception as exc:  # pragma: no cover
+        raise RuntimeError("jax is not installed: the XLA FFI handlers cannot be built on this image") from exc
+    inc = jax.ffi.include_dir()
+    out = os.path.join(_HERE, "libevoxb_ffi.so")
+    cmd = [_nvcc(), "-O2", "-std=c++17", "-Xcompiler", "-fPIC", "-shared", "-I", inc, "-o", out,
+           os.path.join(CSRC, "xla_ffi_handlers.cc"), LIB_PATH, "-Xlinker", "-rpath", "-Xlinker", _HERE]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("building the XLA FFI handlers failed:\n" + res.stdout + res.stderr)
+    return out
+
+
 if __name__ == "__main__":
     import sys
 

@@ -72,3 +72,14 @@ def test_product_never_imports_the_oracle():
                 text = open(os.path.join(root, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", text, flags=re.M), f
                 assert "liboracle" not in text, f
+
+
+def test_jax_binding_says_why_it_cannot_load():
+    """The JAX side is shipped but cannot run here (no jax): importing it must say so, not fail obscurely."""
+    try:
+        import jax  # noqa: F401
+    except ImportError:
+        with pytest.raises(ImportError, match="needs jax/jaxlib"):
+            import evox_myc_b200.jax_ffi  # noqa: F401
+    else:  # pragma: no cover
+        pytest.skip("jax is installed: the binding can be exercised for real")

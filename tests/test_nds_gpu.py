@@ -131,3 +131,35 @@ def test_config2_full_size_properties(n, m):
     # permutation invariance at full size
     p = np.random.default_rng(5).permutation(n)
     assert np.array_equal(_gpu_rank(x[p]), got[p])
+
+
+def test_config4_full_size():
+    """BASELINE config 4 at full size (N = 262144, M = 5): ranks and survivor order against the C oracle
+    (about 15 s of host time), plus properties that need no oracle."""
+    import evox_myc_b200 as e
+    from oracle import c_oracle
+
+    n, m = 262144, 5
+    x = h.uniform(n, m, 52)
+    order, rank, crowd = e.nsga2_select(x, n // 2, return_details=True)
+    w_order, w_rank, w_crowd = c_oracle.nsga2_select(x, n // 2)
+    assert np.array_equal(rank, w_rank)
+    assert np.array_equal(order, w_order)
+    fin = np.isfinite(w_crowd)
+    assert np.array_equal(np.isfinite(crowd), fin)
+    np.testing.assert_allclose(crowd[fin], w_crowd[fin], rtol=1e-6, atol=0)
+    # size-independent properties: every rank class is an antichain's worth of work -- check the cheap ones
+    assert rank.min() == 0 and len(np.unique(rank)) == rank.max() + 1        # no empty front
+    assert len(np.unique(order)) == n // 2                                    # survivors are distinct rows
+    assert rank[order].max() <= np.sort(rank)[n // 2]                         # nobody beyond the cut-off rank
+    p = np.random.default_rng(9).permutation(n)
+    assert np.array_equal(e.non_dominated_sort(x[p]), rank[p])                # permutation invariance
+
+
+def test_odd_large_size_many_chunks():
+    """N not a multiple of anything, 74 column chunks (exercises the 4-entries-per-lane prefix variant)."""
+    import evox_myc_b200 as e
+    from oracle import c_oracle
+
+    x = h.nasty(150001, 4, 53)
+    assert np.array_equal(e.non_dominated_sort(x), c_oracle.non_dominated_sort(x))
