@@ -7,7 +7,7 @@
 // scatter -> grid sync.  Keys are not stored: `key(seg, row)` recomputes the 32-bit key of the row an
 // index refers to (the rows are small and L2-resident), so only indices move.
 // Index buffers are laid out [seg][cap]; the source of the first pass may be one list shared by all
-// segments (`src_shared`) or absent (identity).
+// segments (`src_shared`) or absent (identity: position p of segment s stands for index s * cap + p).
 #pragma once
 
 #include <cooperative_groups.h>
@@ -46,7 +46,7 @@ __device__ void coop_radix_pass(cooperative_groups::grid_group &grid, CoopSortSm
         for (int it = 0; it < kCoopItems; ++it) {
             const int p = tile * kCoopTile + it * 256 + threadIdx.x;
             if (p < n) {
-                const uint32_t row = s ? __ldcg(s + p) : (uint32_t)p;
+                const uint32_t row = s ? __ldcg(s + p) : (uint32_t)(seg * cap + p);
                 atomicAdd(&sm.hist[(key(seg, row) >> shift) & 0xffu], 1u);
             }
         }
@@ -90,7 +90,7 @@ __device__ void coop_radix_pass(cooperative_groups::grid_group &grid, CoopSortSm
         for (int it = 0; it < kCoopItems; ++it) {
             const int p = wbase + it * 32 + lane;
             const bool valid = p < n;
-            rows[it] = valid ? (s ? __ldcg(s + p) : (uint32_t)p) : 0u;
+            rows[it] = valid ? (s ? __ldcg(s + p) : (uint32_t)(seg * cap + p)) : 0u;
             dig[it] = valid ? ((key(seg, rows[it]) >> shift) & 0xffu) : 0x100u;
             const uint32_t peers = __match_any_sync(0xffffffffu, dig[it]);
             const uint32_t dd = dig[it] & 0xffu;

@@ -213,6 +213,7 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     __shared__ float xs[kTileRows][K];
     __shared__ int us[kTileRows];
     __shared__ __align__(16) uint32_t stage[kBuildThreads / 32][32][kC];  // per warp: 32 rows x 4 ballot words
+    __shared__ float rb_min1[kTileRows / 32], rb_max1[kTileRows / 32];     // band of objective 1 per 32-row block
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
 
@@ -284,8 +285,37 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     const bool need_uid = !(row_umax < col_umin);
     uint32_t(*st)[kC] = stage[warp];
 
-#define EVOXB_TRI_ROWS(WITH_UID)                                                                            \
-    for (int rb = 0; rb < kTileRows; rb += 32) {                                                            \
+    // Bands of objective 1 (rows inside a 1024-slab are ordered by it, presort.cuh): smallest / largest
+    // value of every 32-row block and of this warp's 128 columns.  fminf / fmaxf skip NaN; rows and
+    // columns holding a NaN are rejected by the uid test, which is always active when one is present.
+    float c_min1 = 0.0f, c_max1 = 0.0f;
+    if (M > 1) {
+        c_min1 = fminf(fminf(xj[0][0], xj[1][0]), fminf(xj[2][0], xj[3][0]));
+        c_max1 = fmaxf(fmaxf(xj[0][0], xj[1][0]), fmaxf(xj[2][0], xj[3][0]));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            c_min1 = fminf(c_min1, __shfl_xor_sync(0xffffffffu, c_min1, o));
+            c_max1 = fmaxf(c_max1, __shfl_xor_sync(0xffffffffu, c_max1, o));
+        }
+        if (warp < kTileRows / 32) {
+            float lo = xs[warp * 32 + lane][0], hi = lo;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+                hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+            }
+            if (lane == 0) {
+                rb_min1[warp] = lo;
+                rb_max1[warp] = hi;
+            }
+        }
+        __syncthreads();
+    }
+
+    // One 32-row block against this warp's 128 columns.  WITH_UID: keep the uid compare.  FIRST: index of
+    // the first objective still compared (1 = objective 1's compare is known to hold and is dropped).
+#define EVOXB_TRI_BLOCK(WITH_UID, FIRST)                                                                    \
+    {                                                                                                       \
         _Pragma("unroll") for (int ii = 0; ii < 32; ++ii) {                                                 \
             float xi[K];                                                                                    \
             _Pragma("unroll") for (int k = 0; k < K; ++k) xi[k] = xs[rb + ii][k];                           \
@@ -294,7 +324,7 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
             _Pragma("unroll") for (int c = 0; c < kC; ++c) {                                                \
                 bool p = WITH_UID ? (ui < uj[c]) : true;                                                    \
                 if (M > 1) {                                                                                \
-                    _Pragma("unroll") for (int k = 0; k < K; ++k) p = p && (xi[k] <= xj[c][k]);             \
+                    _Pragma("unroll") for (int k = FIRST; k < K; ++k) p = p && (xi[k] <= xj[c][k]);         \
                 }                                                                                           \
                 b[c] = __ballot_sync(0xffffffffu, p);                                                       \
             }                                                                                               \
@@ -302,18 +332,27 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
             if (lane == 0) *reinterpret_cast<uint4 *>(st[ii]) = make_uint4(b[0], b[1], b[2], b[3]);         \
         }                                                                                                   \
         __syncwarp();                                                                                       \
-        const uint4 v = *reinterpret_cast<const uint4 *>(st[lane]);                                         \
+        v = *reinterpret_cast<const uint4 *>(st[lane]);                                                     \
         __syncwarp();                                                                                       \
-        const int64_t r = tile_row0 + rb + lane;                                                            \
-        if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = v;                      \
     }
 
-    if (need_uid) {
-        EVOXB_TRI_ROWS(true)
-    } else {
-        EVOXB_TRI_ROWS(false)
+    for (int rb = 0; rb < kTileRows; rb += 32) {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        // no row of the block can satisfy x_i1 <= x_j1 for any column of the warp: the words stay zero
+        const bool dead = (M > 1) && (rb_min1[rb >> 5] > c_max1);
+        // every row of the block satisfies it for every column: the compare is dropped
+        const bool sure = (M > 1) && (rb_max1[rb >> 5] <= c_min1);
+        if (!dead) {
+            if (need_uid) {
+                if (sure) EVOXB_TRI_BLOCK(true, 1) else EVOXB_TRI_BLOCK(true, 0)
+            } else {
+                if (sure) EVOXB_TRI_BLOCK(false, 1) else EVOXB_TRI_BLOCK(false, 0)
+            }
+        }
+        const int64_t r = tile_row0 + rb + lane;
+        if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = v;
     }
-#undef EVOXB_TRI_ROWS
+#undef EVOXB_TRI_BLOCK
 }
 
 // cm == nullptr: the whole matrix on one GPU.  Otherwise only the column chunks of *cm are built and a

@@ -51,7 +51,8 @@ __global__ void __launch_bounds__(256)
 presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, PresortPasses passes,
                     uint32_t *__restrict__ perm_a, uint32_t *__restrict__ perm_b, uint32_t *__restrict__ hist_g,
                     int *__restrict__ tile_max, int *__restrict__ hp, float *__restrict__ xt, int *__restrict__ perm_out,
-                    int *__restrict__ uid_row, int *__restrict__ uid_col) {
+                    int *__restrict__ uid_row, int *__restrict__ uid_col, int *__restrict__ uid_row_q,
+                    int *__restrict__ uid_col_q, uint32_t *__restrict__ slab_hist) {
     __shared__ CoopSortSmem csm;
     __shared__ uint32_t sh_warp[8];
     __shared__ int sh_carry;
@@ -111,8 +112,7 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
         }
     }
     grid.sync();
-    // ---- uid = 1 + latest head at or before p; sorted objective-major copy; permutation as int ----
-    const float nanv = __int_as_float(0x7fc00000);
+    // ---- uid = 1 + latest head at or before p (still indexed by the (key_0, S') position) ----
     for (int tile = blockIdx.x; tile < ptiles; tile += gridDim.x) {
         int c = -1;
         for (int t = threadIdx.x; t < tile; t += 256) c = max(c, __ldcg(tile_max + t));
@@ -156,17 +156,52 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
             if (p >= npad) continue;
             const bool bad = __ldcg(uid_col + p) != 0;
             const int u = max(before, loc[e]) + 1;
-            uid_row[p] = bad ? 0x7fffffff : u;
-            uid_col[p] = bad ? 0 : u;
-            if (p < n) {
-                const uint32_t row = src ? __ldcg(src + p) : (uint32_t)p;
-                perm_out[p] = (int)row;
-                for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = x[(int64_t)row * m + k];
-            } else {
-                for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = nanv;
-            }
+            uid_row_q[p] = bad ? 0x7fffffff : u;
+            uid_col_q[p] = bad ? 0 : u;
         }
         __syncthreads();
+    }
+    grid.sync();
+
+    // ---- order inside every 1024-slab by objective 1 ----
+    // The predicate (uid_i < uid_j) & all_{k>=1}(x_ik <= x_jk) does not depend on where rows sit, and a
+    // row can only dominate rows of its own slab or of later slabs (uid is monotone in the (key_0, S')
+    // order), so the order INSIDE a slab is free.  Sorting it by objective 1 gives every run of 32 / 128
+    // consecutive positions a narrow band of x_1, which lets the build kernel skip (rows, columns)
+    // blocks whose bands cannot satisfy x_i1 <= x_j1, and drop that compare where they always do.
+    // The payload is the position q in the (key_0, S') order; positions >= n sort last in their slab.
+    uint32_t *slab0 = dst;                                   // the free one of perm_a / perm_b
+    uint32_t *slab1 = reinterpret_cast<uint32_t *>(hp);      // heads are no longer needed
+    const uint32_t *slab = nullptr;                          // nullptr = identity
+    if (m >= 2) {
+        const uint32_t *gperm = src;
+        uint32_t *sd = slab0;
+        for (int shift = 0; shift < 32; shift += 8) {
+            auto key = [=](int, uint32_t q) -> uint32_t {
+                if ((int)q >= n) return 0xffffffffu;
+                const uint32_t row = gperm ? __ldcg(gperm + q) : q;
+                return float_to_key(x[(int64_t)row * m + 1]);
+            };
+            coop_radix_pass(grid, csm, key, npad / 1024, 1024, 1024, slab, false, sd, slab_hist, shift);
+            slab = sd;
+            sd = (sd == slab0) ? slab1 : slab0;
+        }
+    }
+
+    // ---- final layout: sorted objective-major copy, permutation, uids ----
+    const float nanv = __int_as_float(0x7fc00000);
+    for (int p = blockIdx.x * 256 + threadIdx.x; p < npad; p += gridDim.x * 256) {
+        const int q = slab ? (int)__ldcg(slab + p) : p;
+        uid_row[p] = __ldcg(uid_row_q + q);
+        uid_col[p] = __ldcg(uid_col_q + q);
+        if (q < n) {
+            const uint32_t row = src ? __ldcg(src + q) : (uint32_t)q;
+            perm_out[p] = (int)row;
+            for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = x[(int64_t)row * m + k];
+        } else {
+            perm_out[p] = -1;
+            for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = nanv;
+        }
     }
 }
 
