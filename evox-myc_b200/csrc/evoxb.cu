@@ -61,7 +61,6 @@ struct NdsLayout {
     int *uid_col;
     int *uid_row_q;  // uids indexed by the (key_0, S') position, before the within-slab reordering
     int *uid_col_q;
-    uint32_t *slab_hist;
     // multi-GPU (column chunks owned cyclically): nranks == 1 means the whole matrix lives here
     ChunkMap cm;
     int nranks, slice_chunks;
@@ -105,7 +104,6 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         L.uid_col = c.take<int>((size_t)L.npad);
         L.uid_row_q = c.take<int>((size_t)L.npad);
         L.uid_col_q = c.take<int>((size_t)L.npad);
-        L.slab_hist = c.take<uint32_t>((size_t)(L.npad / 1024) * kRadix);
     }
     if (sharded) {
         L.send_bits = c.take<uint32_t>((size_t)L.slice_chunks * kChunkWords);
@@ -174,9 +172,8 @@ static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &
     uint32_t *pa = L.sb.vals[0], *pb = L.sb.vals[1], *hist = L.sb.hist;
     int *tile_max = L.tile_max, *hp = L.hp, *perm = L.perm, *ur = L.uid_row, *uc = L.uid_col;
     int *urq = L.uid_row_q, *ucq = L.uid_col_q;
-    uint32_t *shist = L.slab_hist;
     float *xt = L.xt;
-    void *args[] = {&x, &nn, &mm, &npad, &pp, &pa, &pb, &hist, &tile_max, &hp, &xt, &perm, &ur, &uc, &urq, &ucq, &shist};
+    void *args[] = {&x, &nn, &mm, &npad, &pp, &pa, &pb, &hist, &tile_max, &hp, &xt, &perm, &ur, &uc, &urq, &ucq};
     EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)presort_coop_kernel, dim3(blocks), dim3(256), args, 0, s));
     ++g_launches;
     return 0;

@@ -40,6 +40,7 @@ __device__ __forceinline__ unsigned long long sum_tail_keys(const float *__restr
 // launch marks the heads of equal-(key_0, S') runs, scans them into uids and writes the sorted
 // objective-major copy, so the build kernel can start right behind it.
 constexpr int kMaxPasses = 12;
+constexpr int kSlab = 1024;  // positions per slab = columns per build tile
 
 struct PresortPasses {
     int count;
@@ -52,10 +53,12 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
                     uint32_t *__restrict__ perm_a, uint32_t *__restrict__ perm_b, uint32_t *__restrict__ hist_g,
                     int *__restrict__ tile_max, int *__restrict__ hp, float *__restrict__ xt, int *__restrict__ perm_out,
                     int *__restrict__ uid_row, int *__restrict__ uid_col, int *__restrict__ uid_row_q,
-                    int *__restrict__ uid_col_q, uint32_t *__restrict__ slab_hist) {
+                    int *__restrict__ uid_col_q) {
     __shared__ CoopSortSmem csm;
     __shared__ uint32_t sh_warp[8];
     __shared__ int sh_carry;
+    __shared__ uint32_t slab_key[kSlab];
+    __shared__ uint16_t slab_idx[kSlab];
     namespace cgx = cooperative_groups;
     cgx::grid_group grid = cgx::this_grid();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -169,39 +172,59 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
     // order), so the order INSIDE a slab is free.  Sorting it by objective 1 gives every run of 32 / 128
     // consecutive positions a narrow band of x_1, which lets the build kernel skip (rows, columns)
     // blocks whose bands cannot satisfy x_i1 <= x_j1, and drop that compare where they always do.
-    // The payload is the position q in the (key_0, S') order; positions >= n sort last in their slab.
-    uint32_t *slab0 = dst;                                   // the free one of perm_a / perm_b
-    uint32_t *slab1 = reinterpret_cast<uint32_t *>(hp);      // heads are no longer needed
-    const uint32_t *slab = nullptr;                          // nullptr = identity
-    if (m >= 2) {
-        const uint32_t *gperm = src;
-        uint32_t *sd = slab0;
-        for (int shift = 0; shift < 32; shift += 8) {
-            auto key = [=](int, uint32_t q) -> uint32_t {
-                if ((int)q >= n) return 0xffffffffu;
-                const uint32_t row = gperm ? __ldcg(gperm + q) : q;
-                return float_to_key(x[(int64_t)row * m + 1]);
-            };
-            coop_radix_pass(grid, csm, key, npad / 1024, 1024, 1024, slab, false, sd, slab_hist, shift);
-            slab = sd;
-            sd = (sd == slab0) ? slab1 : slab0;
-        }
-    }
-
-    // ---- final layout: sorted objective-major copy, permutation, uids ----
+    // One CTA per slab, bitonic network in shared memory on (key, position) pairs -- positions make the
+    // order total, so the result is deterministic.  Positions >= n carry the largest key and therefore
+    // stay at the end of the last slab.
     const float nanv = __int_as_float(0x7fc00000);
-    for (int p = blockIdx.x * 256 + threadIdx.x; p < npad; p += gridDim.x * 256) {
-        const int q = slab ? (int)__ldcg(slab + p) : p;
-        uid_row[p] = __ldcg(uid_row_q + q);
-        uid_col[p] = __ldcg(uid_col_q + q);
-        if (q < n) {
-            const uint32_t row = src ? __ldcg(src + q) : (uint32_t)q;
-            perm_out[p] = (int)row;
-            for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = x[(int64_t)row * m + k];
-        } else {
-            perm_out[p] = -1;
-            for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = nanv;
+    const int nslabs = npad / kSlab;
+    for (int slab = blockIdx.x; slab < nslabs; slab += gridDim.x) {
+        const int base = slab * kSlab;
+        auto row_of = [&](int q) -> uint32_t { return src ? __ldcg(src + q) : (uint32_t)q; };
+        for (int level = 1; level <= 1 && level < m; ++level) {  // (a second level on objective 2 was measured: no gain)
+            // keys of this level, gathered through the order reached so far
+            for (int t = threadIdx.x; t < kSlab; t += 256) {
+                const int q = base + (level == 1 ? t : (int)slab_idx[t]);
+                slab_key[t] = (q < n) ? float_to_key(x[(int64_t)row_of(q) * m + level]) : 0xffffffffu;
+                if (level == 1) slab_idx[t] = (uint16_t)t;
+            }
+            __syncthreads();
+            const int span = (level == 1) ? kSlab : 128;  // level 2 sorts every 128-band on its own
+            for (int k = 2; k <= span; k <<= 1) {
+                for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int u = threadIdx.x + h * 256;  // 512 compare-exchanges per step
+                        const int i = ((u & ~(j - 1)) << 1) | (u & (j - 1));
+                        const int l = i | j;
+                        const uint32_t ki = slab_key[i], kl = slab_key[l];
+                        const uint16_t ii = slab_idx[i], il = slab_idx[l];
+                        const bool up = (i & k) == 0 || k == span;  // the last merge leaves every block ascending
+                        const bool gt = ki > kl || (ki == kl && ii > il);
+                        if (gt == up) {
+                            slab_key[i] = kl; slab_key[l] = ki;
+                            slab_idx[i] = il; slab_idx[l] = ii;
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
         }
+        // ---- final layout of the slab: sorted objective-major copy, permutation, uids ----
+        for (int t = threadIdx.x; t < kSlab; t += 256) {
+            const int p = base + t;
+            const int q = (m >= 2) ? base + (int)slab_idx[t] : p;
+            uid_row[p] = __ldcg(uid_row_q + q);
+            uid_col[p] = __ldcg(uid_col_q + q);
+            if (q < n) {
+                const uint32_t row = row_of(q);
+                perm_out[p] = (int)row;
+                for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = x[(int64_t)row * m + k];
+            } else {
+                perm_out[p] = -1;
+                for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = nanv;
+            }
+        }
+        __syncthreads();
     }
 }
 
