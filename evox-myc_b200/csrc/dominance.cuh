@@ -208,7 +208,8 @@ inline TriGrid make_tri_grid(int64_t npad, int64_t n_rows) {
 template <int M>
 __global__ void __launch_bounds__(kBuildThreads)
 dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows, const int *__restrict__ uid_row,
-                           const int *__restrict__ uid_col, uint32_t *__restrict__ D, int64_t row_words, TriGrid g) {
+                           const int *__restrict__ uid_col, const float *__restrict__ tile_min1,
+                           const float *__restrict__ tile_max1, uint32_t *__restrict__ D, int64_t row_words, TriGrid g) {
     constexpr int K = (M > 1) ? (M - 1) : 1;  // objectives 1..M-1 are compared
     __shared__ float xs[kTileRows][K];
     __shared__ int us[kTileRows];
@@ -246,12 +247,23 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     const int64_t col_base = tile_col0 + warp * (kC * 32);
     const int64_t word_base = word0 + warp * kC;
 
-    if (tile_col0 + kTileCols - 1 <= tile_row0) {  // entirely on or left of the diagonal: all zero
-        for (int rb = 0; rb < kTileRows; rb += 32) {
-            const int64_t r = tile_row0 + rb + lane;
-            if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = make_uint4(0u, 0u, 0u, 0u);
+    // Tile-level test on objective 1 (rows inside a chunk are ordered by it, so a 1024-tile is a band of
+    // x_1; presort.cuh): if every row's x_1 exceeds every column's, nothing in the tile can dominate.
+    // (A column tile of the rows' own chunk may lie "left" of the rows: inside a chunk positions carry no
+    // order, so such tiles are computed like any other.)
+    bool sure1 = false;  // every row's x_1 <= every column's x_1: that compare is dropped for the tile
+    if (M > 1) {
+        const int rt1024 = (int)(tile_row0 / kTileCols);
+        const float r_lo = tile_min1[rt1024], r_hi = tile_max1[rt1024];
+        const float c_lo = tile_min1[ct], c_hi = tile_max1[ct];
+        if (r_lo > c_hi) {
+            for (int rb = 0; rb < kTileRows; rb += 32) {
+                const int64_t r = tile_row0 + rb + lane;
+                if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = make_uint4(0u, 0u, 0u, 0u);
+            }
+            return;
         }
-        return;
+        sure1 = r_hi <= c_lo;
     }
 
     for (int q = threadIdx.x; q < kTileRows * K; q += kBuildThreads) {
@@ -285,20 +297,21 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     const bool need_uid = !(row_umax < col_umin);
     uint32_t(*st)[kC] = stage[warp];
 
-    // Bands of objective 1 (rows inside a 1024-slab are ordered by it, presort.cuh): smallest / largest
+    // Bands of objective 2 (rows inside a 1024-tile are ordered by it, presort.cuh): smallest / largest
     // value of every 32-row block and of this warp's 128 columns.  fminf / fmaxf skip NaN; rows and
     // columns holding a NaN are rejected by the uid test, which is always active when one is present.
+    constexpr int kB = (K > 1) ? 1 : 0;  // index of objective 2 in xs / xj
     float c_min1 = 0.0f, c_max1 = 0.0f;
-    if (M > 1) {
-        c_min1 = fminf(fminf(xj[0][0], xj[1][0]), fminf(xj[2][0], xj[3][0]));
-        c_max1 = fmaxf(fmaxf(xj[0][0], xj[1][0]), fmaxf(xj[2][0], xj[3][0]));
+    if (K > 1) {
+        c_min1 = fminf(fminf(xj[0][kB], xj[1][kB]), fminf(xj[2][kB], xj[3][kB]));
+        c_max1 = fmaxf(fmaxf(xj[0][kB], xj[1][kB]), fmaxf(xj[2][kB], xj[3][kB]));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             c_min1 = fminf(c_min1, __shfl_xor_sync(0xffffffffu, c_min1, o));
             c_max1 = fmaxf(c_max1, __shfl_xor_sync(0xffffffffu, c_max1, o));
         }
         if (warp < kTileRows / 32) {
-            float lo = xs[warp * 32 + lane][0], hi = lo;
+            float lo = xs[warp * 32 + lane][kB], hi = lo;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
@@ -312,9 +325,9 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
         __syncthreads();
     }
 
-    // One 32-row block against this warp's 128 columns.  WITH_UID: keep the uid compare.  FIRST: index of
-    // the first objective still compared (1 = objective 1's compare is known to hold and is dropped).
-#define EVOXB_TRI_BLOCK(WITH_UID, FIRST)                                                                    \
+    // One 32-row block against this warp's 128 columns.  WITH_UID: keep the uid compare.  DROP: bit k set =
+    // the compare of objective k+1 is known to hold for every pair of the block and is dropped.
+#define EVOXB_TRI_BLOCK(WITH_UID, DROP)                                                                    \
     {                                                                                                       \
         _Pragma("unroll") for (int ii = 0; ii < 32; ++ii) {                                                 \
             float xi[K];                                                                                    \
@@ -324,7 +337,8 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
             _Pragma("unroll") for (int c = 0; c < kC; ++c) {                                                \
                 bool p = WITH_UID ? (ui < uj[c]) : true;                                                    \
                 if (M > 1) {                                                                                \
-                    _Pragma("unroll") for (int k = FIRST; k < K; ++k) p = p && (xi[k] <= xj[c][k]);         \
+                    _Pragma("unroll") for (int k = 0; k < K; ++k)                                           \
+                        if (!((DROP) >> k & 1)) p = p && (xi[k] <= xj[c][k]);                               \
                 }                                                                                           \
                 b[c] = __ballot_sync(0xffffffffu, p);                                                       \
             }                                                                                               \
@@ -338,15 +352,21 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
 
     for (int rb = 0; rb < kTileRows; rb += 32) {
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        // no row of the block can satisfy x_i1 <= x_j1 for any column of the warp: the words stay zero
-        const bool dead = (M > 1) && (rb_min1[rb >> 5] > c_max1);
+        // no row of the block can satisfy x_i2 <= x_j2 for any column of the warp: the words stay zero
+        const bool dead = (K > 1) && (rb_min1[rb >> 5] > c_max1);
         // every row of the block satisfies it for every column: the compare is dropped
-        const bool sure = (M > 1) && (rb_max1[rb >> 5] <= c_min1);
+        const bool sure2 = (K > 1) && (rb_max1[rb >> 5] <= c_min1);
         if (!dead) {
+            // Dropping a compare needs its own copy of the unrolled loop; copies are only worth their
+            // instruction-cache footprint where they save a sizeable share of the work: not near the
+            // diagonal (uid test active, rare) and not for many objectives.
             if (need_uid) {
-                if (sure) EVOXB_TRI_BLOCK(true, 1) else EVOXB_TRI_BLOCK(true, 0)
+                EVOXB_TRI_BLOCK(true, 0)
+            } else if (K > 5) {
+                EVOXB_TRI_BLOCK(false, 0)
             } else {
-                if (sure) EVOXB_TRI_BLOCK(false, 1) else EVOXB_TRI_BLOCK(false, 0)
+                if (sure1) { if (sure2) EVOXB_TRI_BLOCK(false, 3) else EVOXB_TRI_BLOCK(false, 1) }
+                else       { if (sure2) EVOXB_TRI_BLOCK(false, 2) else EVOXB_TRI_BLOCK(false, 0) }
             }
         }
         const int64_t r = tile_row0 + rb + lane;
@@ -358,8 +378,8 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
 // cm == nullptr: the whole matrix on one GPU.  Otherwise only the column chunks of *cm are built and a
 // matrix row holds cm->nlocal * 128 words.
 inline int launch_dominance_build_tri(const float *xt, int64_t npad, int64_t n_rows, int m, const int *uid_row,
-                                      const int *uid_col, uint32_t *D, int64_t row_words, cudaStream_t s,
-                                      const ChunkMap *cm = nullptr) {
+                                      const int *uid_col, const float *tile_min1, const float *tile_max1, uint32_t *D,
+                                      int64_t row_words, cudaStream_t s, const ChunkMap *cm = nullptr) {
     if (n_rows <= 0) return 0;
     TriGrid g = make_tri_grid(npad, n_rows);
     if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
@@ -373,8 +393,8 @@ inline int launch_dominance_build_tri(const float *xt, int64_t npad, int64_t n_r
     }
 #define EVOXB_TRI_CASE(MM)                                                                                     \
     case MM:                                                                                                   \
-        dominance_build_tri_kernel<MM><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, uid_row, uid_col, D,   \
-                                                                      row_words, g);                           \
+        dominance_build_tri_kernel<MM><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, uid_row, uid_col,      \
+                                                                      tile_min1, tile_max1, D, row_words, g);  \
         break;
     switch (m) {
         EVOXB_TRI_CASE(1) EVOXB_TRI_CASE(2) EVOXB_TRI_CASE(3) EVOXB_TRI_CASE(4) EVOXB_TRI_CASE(5) EVOXB_TRI_CASE(6)

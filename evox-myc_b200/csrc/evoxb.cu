@@ -59,8 +59,10 @@ struct NdsLayout {
     int *tile_max;
     int *uid_row;
     int *uid_col;
-    int *uid_row_q;  // uids indexed by the (key_0, S') position, before the within-slab reordering
+    int *uid_row_q;  // uids indexed by the (key_0, S') position, before the within-chunk reordering
     int *uid_col_q;
+    float *tile_min1;  // band of objective 1 of every 1024-tile
+    float *tile_max1;
     // multi-GPU (column chunks owned cyclically): nranks == 1 means the whole matrix lives here
     ChunkMap cm;
     int nranks, slice_chunks;
@@ -104,6 +106,8 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         L.uid_col = c.take<int>((size_t)L.npad);
         L.uid_row_q = c.take<int>((size_t)L.npad);
         L.uid_col_q = c.take<int>((size_t)L.npad);
+        L.tile_min1 = c.take<float>((size_t)(L.npad / 1024));
+        L.tile_max1 = c.take<float>((size_t)(L.npad / 1024));
     }
     if (sharded) {
         L.send_bits = c.take<uint32_t>((size_t)L.slice_chunks * kChunkWords);
@@ -172,8 +176,9 @@ static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &
     uint32_t *pa = L.sb.vals[0], *pb = L.sb.vals[1], *hist = L.sb.hist;
     int *tile_max = L.tile_max, *hp = L.hp, *perm = L.perm, *ur = L.uid_row, *uc = L.uid_col;
     int *urq = L.uid_row_q, *ucq = L.uid_col_q;
+    float *tmin = L.tile_min1, *tmax = L.tile_max1;
     float *xt = L.xt;
-    void *args[] = {&x, &nn, &mm, &npad, &pp, &pa, &pb, &hist, &tile_max, &hp, &xt, &perm, &ur, &uc, &urq, &ucq};
+    void *args[] = {&x, &nn, &mm, &npad, &pp, &pa, &pb, &hist, &tile_max, &hp, &xt, &perm, &ur, &uc, &urq, &ucq, &tmin, &tmax};
     EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)presort_coop_kernel, dim3(blocks), dim3(256), args, 0, s));
     ++g_launches;
     return 0;
@@ -192,7 +197,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         if (int rc = run_presort(fitness, n, m, L, s)) return rc;
         perm = L.perm;
         prof.mark("dominance_build", s);
-        if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.D, L.row_words, s)) return rc;
+        if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, L.row_words, s)) return rc;
     } else {
         transpose_pad_kernel<<<(unsigned)div_up(L.npad, 256), 256, 0, s>>>(fitness, n, m, L.npad, L.xt);
         EVOXB_LAUNCH_CHECK("transpose_pad_kernel");
@@ -287,7 +292,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
     if (int rc = run_presort(fitness, n, m, L, s)) return rc;
 
     prof.mark("dominance_build", s);
-    if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.D, L.row_words, s, &L.cm)) return rc;
+    if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, L.row_words, s, &L.cm)) return rc;
 
     const void *p2p_kern = L.nchunks <= 32    ? (const void *)peel_p2p_kernel<1>
                            : L.nchunks <= 128 ? (const void *)peel_p2p_kernel<4>

@@ -40,7 +40,8 @@ __device__ __forceinline__ unsigned long long sum_tail_keys(const float *__restr
 // launch marks the heads of equal-(key_0, S') runs, scans them into uids and writes the sorted
 // objective-major copy, so the build kernel can start right behind it.
 constexpr int kMaxPasses = 12;
-constexpr int kSlab = 1024;  // positions per slab = columns per build tile
+constexpr int kSlab = 1024;   // columns per build tile
+constexpr int kChunk = 4096;  // positions per chunk (= csrc/peel.cuh kChunkCols): reordering stays inside a chunk
 
 struct PresortPasses {
     int count;
@@ -53,12 +54,13 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
                     uint32_t *__restrict__ perm_a, uint32_t *__restrict__ perm_b, uint32_t *__restrict__ hist_g,
                     int *__restrict__ tile_max, int *__restrict__ hp, float *__restrict__ xt, int *__restrict__ perm_out,
                     int *__restrict__ uid_row, int *__restrict__ uid_col, int *__restrict__ uid_row_q,
-                    int *__restrict__ uid_col_q) {
+                    int *__restrict__ uid_col_q, float *__restrict__ tile_min1, float *__restrict__ tile_max1) {
     __shared__ CoopSortSmem csm;
     __shared__ uint32_t sh_warp[8];
     __shared__ int sh_carry;
-    __shared__ uint32_t slab_key[kSlab];
-    __shared__ uint16_t slab_idx[kSlab];
+    __shared__ uint32_t slab_key[kChunk];
+    __shared__ uint16_t slab_idx[kChunk];
+    __shared__ float band_lo[8], band_hi[8];
     namespace cgx = cooperative_groups;
     cgx::grid_group grid = cgx::this_grid();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -166,34 +168,36 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
     }
     grid.sync();
 
-    // ---- order inside every 1024-slab by objective 1 ----
+    // ---- order inside every 4096-chunk: by objective 1, then inside every 1024-tile by objective 2 ----
     // The predicate (uid_i < uid_j) & all_{k>=1}(x_ik <= x_jk) does not depend on where rows sit, and a
-    // row can only dominate rows of its own slab or of later slabs (uid is monotone in the (key_0, S')
-    // order), so the order INSIDE a slab is free.  Sorting it by objective 1 gives every run of 32 / 128
-    // consecutive positions a narrow band of x_1, which lets the build kernel skip (rows, columns)
-    // blocks whose bands cannot satisfy x_i1 <= x_j1, and drop that compare where they always do.
-    // One CTA per slab, bitonic network in shared memory on (key, position) pairs -- positions make the
+    // row can only dominate rows of its own chunk or of later chunks (uid is monotone in the (key_0, S')
+    // order; the peel only assumes "no bits left of the row's own chunk"), so the order INSIDE a chunk is
+    // free.  Sorting it by objective 1 makes each of its four 1024-tiles a band of x_1; sorting each tile
+    // by objective 2 makes every run of 32 / 128 positions in it a narrow band of x_2.  The build kernel
+    // then (a) discards a whole (row tile, column tile) whose x_1 bands cannot match, (b) discards
+    // (32 rows x 128 columns) blocks whose x_2 bands cannot match, (c) drops a compare that always holds.
+    // One CTA per chunk, bitonic network in shared memory on (key, position) pairs -- positions make the
     // order total, so the result is deterministic.  Positions >= n carry the largest key and therefore
-    // stay at the end of the last slab.
+    // stay at the end of the last chunk.
     const float nanv = __int_as_float(0x7fc00000);
-    const int nslabs = npad / kSlab;
-    for (int slab = blockIdx.x; slab < nslabs; slab += gridDim.x) {
-        const int base = slab * kSlab;
+    const int nchunks = npad / kChunk;
+    for (int chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+        const int base = chunk * kChunk;
         auto row_of = [&](int q) -> uint32_t { return src ? __ldcg(src + q) : (uint32_t)q; };
-        for (int level = 1; level <= 1 && level < m; ++level) {  // (a second level on objective 2 was measured: no gain)
+        for (int level = 1; level <= 2 && level < m; ++level) {
             // keys of this level, gathered through the order reached so far
-            for (int t = threadIdx.x; t < kSlab; t += 256) {
+            for (int t = threadIdx.x; t < kChunk; t += 256) {
                 const int q = base + (level == 1 ? t : (int)slab_idx[t]);
                 slab_key[t] = (q < n) ? float_to_key(x[(int64_t)row_of(q) * m + level]) : 0xffffffffu;
                 if (level == 1) slab_idx[t] = (uint16_t)t;
             }
             __syncthreads();
-            const int span = (level == 1) ? kSlab : 128;  // level 2 sorts every 128-band on its own
+            const int span = (level == 1) ? kChunk : kSlab;  // level 2 sorts every 1024-tile on its own
             for (int k = 2; k <= span; k <<= 1) {
                 for (int j = k >> 1; j > 0; j >>= 1) {
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int u = threadIdx.x + h * 256;  // 512 compare-exchanges per step
+                    for (int h = 0; h < kChunk / 512; ++h) {
+                        const int u = threadIdx.x + h * 256;  // kChunk / 2 compare-exchanges per step
                         const int i = ((u & ~(j - 1)) << 1) | (u & (j - 1));
                         const int l = i | j;
                         const uint32_t ki = slab_key[i], kl = slab_key[l];
@@ -209,19 +213,39 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
                 }
             }
         }
-        // ---- final layout of the slab: sorted objective-major copy, permutation, uids ----
-        for (int t = threadIdx.x; t < kSlab; t += 256) {
-            const int p = base + t;
-            const int q = (m >= 2) ? base + (int)slab_idx[t] : p;
-            uid_row[p] = __ldcg(uid_row_q + q);
-            uid_col[p] = __ldcg(uid_col_q + q);
-            if (q < n) {
-                const uint32_t row = row_of(q);
-                perm_out[p] = (int)row;
-                for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = x[(int64_t)row * m + k];
-            } else {
-                perm_out[p] = -1;
-                for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = nanv;
+        // ---- final layout of the chunk: sorted objective-major copy, permutation, uids, x_1 band per tile ----
+        for (int tile = 0; tile < kChunk / kSlab; ++tile) {
+            float lo = __int_as_float(0x7fc00000), hi = lo;  // NaN: "no value yet" (fminf / fmaxf skip it)
+            for (int t = tile * kSlab + threadIdx.x; t < (tile + 1) * kSlab; t += 256) {
+                const int p = base + t;
+                const int q = (m >= 2) ? base + (int)slab_idx[t] : p;
+                uid_row[p] = __ldcg(uid_row_q + q);
+                uid_col[p] = __ldcg(uid_col_q + q);
+                if (q < n) {
+                    const uint32_t row = row_of(q);
+                    perm_out[p] = (int)row;
+                    for (int k = 0; k < m; ++k) {
+                        const float v = x[(int64_t)row * m + k];
+                        xt[(int64_t)k * npad + p] = v;
+                        if (k == 1) { lo = fminf(lo, v); hi = fmaxf(hi, v); }
+                    }
+                } else {
+                    perm_out[p] = -1;
+                    for (int k = 0; k < m; ++k) xt[(int64_t)k * npad + p] = nanv;
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+                hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+            }
+            __syncthreads();
+            if (lane == 0) { band_lo[warp] = lo; band_hi[warp] = hi; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                for (int w = 1; w < 8; ++w) { lo = fminf(lo, band_lo[w]); hi = fmaxf(hi, band_hi[w]); }
+                tile_min1[chunk * (kChunk / kSlab) + tile] = lo;
+                tile_max1[chunk * (kChunk / kSlab) + tile] = hi;
             }
         }
         __syncthreads();
