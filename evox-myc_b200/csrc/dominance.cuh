@@ -329,7 +329,7 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     // the compare of objective k+1 is known to hold for every pair of the block and is dropped.
 #define EVOXB_TRI_BLOCK(WITH_UID, DROP)                                                                    \
     {                                                                                                       \
-        _Pragma("unroll") for (int ii = 0; ii < 32; ++ii) {                                                 \
+        _Pragma("unroll 8") for (int ii = 0; ii < 32; ++ii) {                                               \
             float xi[K];                                                                                    \
             _Pragma("unroll") for (int k = 0; k < K; ++k) xi[k] = xs[rb + ii][k];                           \
             const int ui = WITH_UID ? us[rb + ii] : 0;                                                      \
