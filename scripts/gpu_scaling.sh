@@ -3,7 +3,7 @@ set -x
 OUT=gpurun_out/${1:-scale}
 mkdir -p $OUT
 NG=$(nvidia-smi -L | wc -l)
-timeout 600 python -m pytest tests/test_sharded_gpu.py -m gpu -x -q 2>&1 | tail -4 | tee $OUT/tests.log
+timeout 600 python -m pytest tests/test_sharded_gpu.py -m gpu -x -q -k "${TESTSEL:-multi_gpu}" 2>&1 | tail -4 | tee $OUT/tests.log
 python bench.py --gpus 1 --steps 20 --warmup 3 --no-cpu-baseline > $OUT/bench_n1.json 2> $OUT/bench_n1.err
 for N in 2 4 8; do
   if [ $N -le $NG ]; then
