@@ -136,4 +136,20 @@ __device__ __forceinline__ uint4 ldg_stream_v4(const uint4 *p) {
     return r;
 }
 
+// the same load, predicated in the instruction itself (no branch: a batch of such loads stays in
+// flight together); returns zeros when `fetch` is false
+__device__ __forceinline__ uint4 ldg_stream_v4_if(const uint4 *p, bool fetch) {
+    uint4 r;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred q;\n\t"
+        "setp.ne.u32 q, %5, 0;\n\t"
+        "mov.u32 %0, 0; mov.u32 %1, 0; mov.u32 %2, 0; mov.u32 %3, 0;\n\t"
+        "@q ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];\n\t"
+        "}"
+        : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+        : "l"(p), "r"((unsigned)fetch));
+    return r;
+}
+
 }  // namespace evoxb

@@ -214,8 +214,9 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     const int tri = L.tri ? 1 : 0;
 
     prof.mark("dominator_count", s);
+    const TileBands tb{L.tri ? L.tile_min1 : nullptr, L.tri ? L.tile_max1 : nullptr};
     dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, tri, ChunkMap{0, 1, L.nchunks},
-                                                           L.count);
+                                                           L.count, tb);
     EVOXB_LAUNCH_CHECK("dominator_count_kernel");
 
     prof.mark("peel", s);
@@ -229,7 +230,8 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         int *rk = rank;
         int *list = L.list;
         PeelCtrl *ctrl = L.ctrl;
-        void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl};
+        TileBands tbv = tb;
+        void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl, &tbv};
         EVOXB_CUDA(cudaLaunchCooperativeKernel(peel_kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
     }
@@ -299,9 +301,10 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
                                               : (const void *)peel_p2p_kernel<kMaxChunks / 32>;
     int blocks = 0;
     if (int rc = coop_blocks(p2p_kern, kPeelThreads, 3, &blocks)) return rc;
+    const TileBands tb{L.tile_min1, L.tile_max1};
     prof.mark("dominator_count", s);
     if (L.cm.nlocal > 0) {
-        dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, 1, L.cm, L.count);
+        dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, 1, L.cm, L.count, tb);
         EVOXB_LAUNCH_CHECK("dominator_count_kernel");
     }
 
@@ -318,7 +321,8 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         const int *perm = L.perm;
         uint32_t *mybits = L.send_bits;
         XchgCtx x{comm->peers_dev, comm->rank, comm->nranks, L.slice_chunks};
-        void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &mybits, &x, &fronts};
+        TileBands tbv = tb;
+        void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &mybits, &x, &fronts, &tbv};
         EVOXB_CUDA(cudaLaunchCooperativeKernel(p2p_kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
         return 0;
@@ -339,7 +343,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
             EVOXB_LAUNCH_CHECK("front_expand_kernel");
             if (L.cm.nlocal > 0) {
                 front_subtract_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, (int)n, 1, L.cm, L.list,
-                                                                      L.cnt, L.count);
+                                                                      L.cnt, L.count, tb);
                 EVOXB_LAUNCH_CHECK("front_subtract_kernel");
             }
         }

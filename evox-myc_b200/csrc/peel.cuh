@@ -57,11 +57,23 @@ __device__ __forceinline__ void vc_add8(uint32_t (&pl)[kPlanes], const uint32_t 
 // Shared memory used by one CTA for the cross-warp reduction and the expansion.
 constexpr int kStageRows = 1024;  // member rows resolved per staging round
 
+// Band of objective 1 of every 1024-position tile (presort.cuh).  A (row, 1024-column tile) segment of
+// the matrix is all zero when the row tile's smallest x_1 exceeds the column tile's largest -- the
+// build kernel zero-filled it without looking -- so count and peel do not fetch those 128-byte
+// quarters of a row chunk (predicated loads: no branch, the batch stays in flight).
+struct TileBands {
+    const float *tmin;  // nullptr: no band information (unsorted full-matrix mode)
+    const float *tmax;
+};
+
 struct PeelSmem {
     uint32_t xchg[kPeelWarps / 2][4 * kPlanes][32];  // up to 4 senders per round
     union {
         uint32_t fin[kPlanes][kChunkWords];          // CTA totals, plane-major (expansion)
-        int rows[kStageRows];                        // row ids of the members being streamed
+        struct {
+            int rows[kStageRows];                    // row ids of the members being streamed
+            float rowmin[kStageRows];                // smallest x_1 of each such row's 1024-tile
+        } st;
     };
 };
 
@@ -179,11 +191,13 @@ __device__ __forceinline__ int member_row(const int *__restrict__ list, const Pr
 // adds sign * (column sums) to count[].
 __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_words, const int *__restrict__ list,
                                  const PrefixSmem &ps, int nregions, int64_t t0, int64_t t1, int local_chunk, int chunk,
-                                 int *__restrict__ count, int sign, PeelSmem &sm) {
+                                 int *__restrict__ count, int sign, PeelSmem &sm, TileBands tb) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const uint4 *base = reinterpret_cast<const uint4 *>(D + (int64_t)local_chunk * kChunkWords) + lane;
     const int64_t row_vec = row_words >> 2;  // row stride in uint4
+    // this lane's 128 columns lie in column tile chunk * 4 + lane / 8; +inf = "always fetch"
+    const float col_max = tb.tmax ? tb.tmax[chunk * 4 + (lane >> 3)] : __int_as_float(0x7f800000);
 
     for (int64_t f0 = t0; f0 < t1; f0 += (int64_t)kWarpRowsCap * kPeelWarps) {
         const int64_t f1 = min(t1, f0 + (int64_t)kWarpRowsCap * kPeelWarps);
@@ -196,7 +210,11 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
         for (int64_t g0 = f0; g0 < f1; g0 += kStageRows) {
             const int gn = (int)min((int64_t)kStageRows, f1 - g0);
             // all threads resolve member -> row in parallel (one list-load latency per round)
-            for (int q = threadIdx.x; q < gn; q += kPeelThreads) sm.rows[q] = member_row(list, ps, nregions, g0 + q);
+            for (int q = threadIdx.x; q < gn; q += kPeelThreads) {
+                const int row = member_row(list, ps, nregions, g0 + q);
+                sm.st.rows[q] = row;
+                sm.st.rowmin[q] = tb.tmin ? tb.tmin[row >> 10] : 0.0f;
+            }
             __syncthreads();
             // warp `warp` takes staged members warp, warp + 8, ... in batches of kBatch
             for (int q = warp; q < gn; q += kPeelWarps * kBatch) {
@@ -204,8 +222,10 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
 #pragma unroll
                 for (int b = 0; b < kBatch; ++b) {
                     const int qq = q + b * kPeelWarps;
-                    if (qq < gn) v[b] = ldg_stream_v4(base + (int64_t)sm.rows[qq] * row_vec);
-                    else v[b] = make_uint4(0u, 0u, 0u, 0u);
+                    // a NaN band (a tile of NaN rows only) compares false and is fetched
+                    const int qc = min(qq, gn - 1);
+                    const bool fetch = qq < gn && !(sm.st.rowmin[qc] > col_max);
+                    v[b] = ldg_stream_v4_if(base + (int64_t)sm.st.rows[qc] * row_vec, fetch);
                 }
                 uint32_t w[kBatch];
 #pragma unroll
@@ -290,7 +310,7 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
 // One front (or, with list == nullptr, all rows): the caller has run build_prefix().
 __device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, bool tri, ChunkMap cm,
                                  const int *__restrict__ list, const PrefixSmem &ps, int *__restrict__ count, int sign,
-                                 PeelSmem &sm) {
+                                 PeelSmem &sm, TileBands tb) {
     const long long total = ps.S[cm.nlocal];
     const long long s0 = total * blockIdx.x / gridDim.x;
     const long long s1 = total * (blockIdx.x + 1) / gridDim.x;
@@ -309,7 +329,7 @@ __device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_wor
         const int lc = chunk_order(i, cm.nlocal, tri);
         const int chunk = cm.global(lc);
         if (t1 > t0)
-            accumulate_chunk(D, row_words, list, ps, tri ? chunk + 1 : nchunks, t0, t1, lc, chunk, count, sign, sm);
+            accumulate_chunk(D, row_words, list, ps, tri ? chunk + 1 : nchunks, t0, t1, lc, chunk, count, sign, sm, tb);
         s += t1 - t0;
         ++i;
     }
@@ -318,11 +338,11 @@ __device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_wor
 // K2: count[j] += number of rows in [0, n_rows) that dominate j   (non_dominate.py:61)
 __global__ void __launch_bounds__(kPeelThreads)
 dominator_count_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int64_t n_rows, int tri,
-                       ChunkMap cm, int *__restrict__ count) {
+                       ChunkMap cm, int *__restrict__ count, TileBands tb) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     build_prefix(nullptr, nchunks, n_rows, tri != 0, cm, ps);
-    accumulate_front(D, row_words, nchunks, tri != 0, cm, nullptr, ps, count, +1, sm);
+    accumulate_front(D, row_words, nchunks, tri != 0, cm, nullptr, ps, count, +1, sm, tb);
 }
 
 // Front detection: every j < n with count[j] == 0 joins the front, gets its rank, and drops to -1
@@ -357,10 +377,10 @@ struct PeelCtrl {
 
 // K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).
 template <int kPer>
-__global__ void __launch_bounds__(kPeelThreads)
+__global__ void __launch_bounds__(kPeelThreads, 2)
 peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri,
                        int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm,
-                       int *__restrict__ list, PeelCtrl *__restrict__ ctrl) {
+                       int *__restrict__ list, PeelCtrl *__restrict__ ctrl, TileBands tb) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     cg::grid_group grid = cg::this_grid();
@@ -373,7 +393,7 @@ peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nc
         if (ps.pc[nchunks] == 0) break;  // non_dominate.py:76-78: while any(front)
         if (blockIdx.x == 0)
             for (int c = threadIdx.x; c < nchunks; c += blockDim.x) ctrl->cnt[(r + 1) & 1][c] = 0;
-        accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm);
+        accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm, tb);
         grid.sync();
         ++r;
     }
@@ -442,11 +462,11 @@ front_expand_kernel(const uint32_t *__restrict__ gathered, int nranks, int slice
 // Subtracts the rows of the current front from this GPU's columns.
 __global__ void __launch_bounds__(kPeelThreads)
 front_subtract_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri, ChunkMap cm,
-                      const int *__restrict__ list, const int *__restrict__ cnt, int *__restrict__ count) {
+                      const int *__restrict__ list, const int *__restrict__ cnt, int *__restrict__ count, TileBands tb) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     build_prefix(cnt, nchunks, n, tri != 0, cm, ps);
-    accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm);
+    accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm, tb);
 }
 
 // ---- multi-GPU, fused: the front loop and its exchange in ONE persistent kernel per GPU ---------------
@@ -504,10 +524,11 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 
 template <int kPer>
-__global__ void __launch_bounds__(kPeelThreads)
+__global__ void __launch_bounds__(kPeelThreads, 2)
 peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, ChunkMap cm,
                 int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm, int *__restrict__ list,
-                int *__restrict__ cnt, uint32_t *__restrict__ mybits, XchgCtx x, int *__restrict__ fronts_done) {
+                int *__restrict__ cnt, uint32_t *__restrict__ mybits, XchgCtx x, int *__restrict__ fronts_done,
+                TileBands tb) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     __shared__ int sh_wsum[kPeelThreads / 32];
@@ -624,7 +645,7 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
         // 5. subtract the front's rows from my columns
         build_prefix_t<kPer>(cnt, nchunks, n, true, cm, ps);
         if (ps.pc[nchunks] == 0) break;  // the same bitmask everywhere: every rank stops at the same front
-        accumulate_front(D, row_words, nchunks, true, cm, list, ps, count, -1, sm);
+        accumulate_front(D, row_words, nchunks, true, cm, list, ps, count, -1, sm, tb);
         grid.sync();
         ++r;
     }
