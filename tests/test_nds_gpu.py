@@ -50,7 +50,10 @@ CASES = [
     ("n1025_m3", lambda: h.uniform(1025, 3, 7)),
     ("n4097_m5", lambda: h.uniform(4097, 5, 8)),
     ("n5000_m10", lambda: h.uniform(5000, 10, 9)),
-    ("n3000_m13_generic", lambda: h.uniform(3000, 13, 10)),
+    ("n3000_m13", lambda: h.uniform(3000, 13, 10)),
+    ("n3000_m16", lambda: h.nasty(3000, 16, 18)),
+    ("n2500_m20_full_matrix_mode", lambda: h.nasty(2500, 20, 19)),   # m > 16: unsorted full-matrix kernels
+    ("n5000_m32_full_matrix_mode", lambda: h.uniform(5000, 32, 20)),
     ("grid", lambda: h.integer_grid(6000, 3, 11, levels=8)),
     ("grid_m2", lambda: h.integer_grid(5000, 2, 12, levels=64)),
     ("nasty", lambda: h.nasty(7001, 4, 13)),

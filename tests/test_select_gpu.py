@@ -16,6 +16,7 @@ CASES = [
     ("nasty", lambda: h.nasty(5000, 4, 5), 2500),
     ("dtlz2", lambda: h.dtlz2(8192, 3, 12, 6), 4096),
     ("dtlz2_converged", lambda: h.dtlz2(4096, 3, 12, 7, converged=True), 2048),
+    ("m18_full_matrix_mode", lambda: h.uniform(3000, 18, 12), 1500),
     ("pop_1", lambda: h.uniform(100, 3, 8), 1),
     ("pop_n_minus_1", lambda: h.uniform(100, 3, 9), 99),
     ("config1_pop100", lambda: h.dtlz2(200, 3, 12, 10), 100),
