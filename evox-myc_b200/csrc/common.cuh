@@ -69,26 +69,6 @@ struct Carver {
     size_t total() const { return (off + 255) & ~size_t(255); }
 };
 
-// ---- device info (cached per device) ---------------------------------------------------------
-struct DevInfo {
-    int sms = 0;
-    bool ok = false;
-};
-inline int device_sms(int *sms_out) {
-    static thread_local int cached_dev = -1;
-    static thread_local int cached_sms = 0;
-    int dev = 0;
-    EVOXB_CUDA(cudaGetDevice(&dev));
-    if (dev != cached_dev) {
-        int sms = 0;
-        EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        cached_dev = dev;
-        cached_sms = sms;
-    }
-    *sms_out = cached_sms;
-    return 0;
-}
-
 // ---- stage profiler (events on the caller's stream) -------------------------------------------
 struct Profiler {
     static constexpr int kMax = 24;
@@ -113,7 +93,6 @@ inline Profiler &profiler() {
     static thread_local Profiler p;
     return p;
 }
-extern bool g_profile_enabled;
 extern unsigned long long g_launches;  // kernels launched by this library since load (not thread-safe: a statistic)
 
 // ---- small device helpers ---------------------------------------------------------------------

@@ -19,7 +19,6 @@
 
 namespace evoxb {
 
-bool g_profile_enabled = false;
 unsigned long long g_launches = 0;
 
 struct NcclId {
@@ -129,6 +128,15 @@ static int check_common(const void *fitness, int64_t n, int m) {
     return 0;
 }
 
+// Grid of the persistent peel kernels: all co-resident CTAs (two per SM) when there is bandwidth to
+// win, one per SM when the per-front latency dominates (rows_per_gpu = rows this GPU streams from).
+static int peel_grid_for(int64_t rows_per_gpu, int max_blocks) {
+    const int half = max_blocks / 2;
+    static const char *ev = getenv("EVOXB_PEEL_SMALL_ROWS");  // development knob
+    const int64_t limit = ev ? atoll(ev) : 98304;
+    return (rows_per_gpu <= limit && half >= 1) ? half : max_blocks;
+}
+
 // Largest co-resident grid (capped at `cap_per_sm` CTAs per SM) for a cooperative kernel, cached per
 // (device, kernel).  Every template instance has its own register count, so each is queried itself.
 static int coop_blocks(const void *kern, int threads, int cap_per_sm, int *blocks) {
@@ -211,6 +219,10 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
                                                : (const void *)peel_persistent_kernel<kMaxChunks / 32>;
     int blocks = 0;
     if (int rc = coop_blocks(peel_kern, kPeelThreads, 3, &blocks)) return rc;
+    // Small populations are bound by the per-front latency, of which the grid-wide syncs and the
+    // per-CTA flush are a part: one CTA per SM instead of two is faster there (measured on the B200:
+    // N = 32768: 1.11 -> 0.95 ms, N = 65536: 1.54 -> 1.44 ms, N = 262144: 1.24 -> 1.68 ms).
+    const int peel_blocks = peel_grid_for(n, blocks);
     const int tri = L.tri ? 1 : 0;
 
     prof.mark("dominator_count", s);
@@ -232,7 +244,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         PeelCtrl *ctrl = L.ctrl;
         TileBands tbv = tb;
         void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl, &tbv};
-        EVOXB_CUDA(cudaLaunchCooperativeKernel(peel_kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
+        EVOXB_CUDA(cudaLaunchCooperativeKernel(peel_kern, dim3(peel_blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
     }
     return 0;
@@ -312,18 +324,17 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
     const size_t slice_words = (size_t)L.slice_chunks * kChunkWords;
     if (comm->p2p && (size_t)L.nranks * slice_words <= (size_t)kXchgSliceWordsCap) {
         // fused path: one persistent kernel per GPU exchanges the front bitmask over peer memory
-        EVOXB_CUDA(cudaMemsetAsync(L.send_bits, 0, sizeof(uint32_t) * slice_words, s));
         const uint32_t *D = L.D;
         int64_t row_words = L.row_words;
         int nchunks = L.nchunks, nn = (int)n;
         ChunkMap cm = L.cm;
         int *count = L.count, *rk = rank, *list = L.list, *cnt = L.cnt, *fronts = comm->fronts_dev;
         const int *perm = L.perm;
-        uint32_t *mybits = L.send_bits;
         XchgCtx x{comm->peers_dev, comm->rank, comm->nranks, L.slice_chunks};
         TileBands tbv = tb;
-        void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &mybits, &x, &fronts, &tbv};
-        EVOXB_CUDA(cudaLaunchCooperativeKernel(p2p_kern, dim3(blocks), dim3(kPeelThreads), args, 0, s));
+        void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &x, &fronts, &tbv};
+        EVOXB_CUDA(cudaLaunchCooperativeKernel(p2p_kern, dim3(peel_grid_for(n / L.nranks, blocks)), dim3(kPeelThreads), args,
+                                               0, s));
         ++g_launches;
         return 0;
     }

@@ -489,7 +489,7 @@ struct XchgHeader {            // at the start of every rank's exchange buffer
     unsigned int epoch;        // last epoch this rank completed (persists across calls)
     unsigned int error;        // 1 = a wait timed out
     unsigned int pad0[62];
-    unsigned int flags[64];    // (unused by the tagged protocol)
+    unsigned int reserved[64];
     uint2 hb[2][16];           // hb[parity][q] = {0, epoch}: sender q has started delivering that epoch
 };
 static_assert(sizeof(XchgHeader) == 768, "header layout");
@@ -527,7 +527,7 @@ template <int kPer>
 __global__ void __launch_bounds__(kPeelThreads, 2)
 peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, ChunkMap cm,
                 int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm, int *__restrict__ list,
-                int *__restrict__ cnt, uint32_t *__restrict__ mybits, XchgCtx x, int *__restrict__ fronts_done,
+                int *__restrict__ cnt, XchgCtx x, int *__restrict__ fronts_done,
                 TileBands tb) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
