@@ -353,18 +353,30 @@ __device__ void collect_front(int *__restrict__ count, int n, int r, int *__rest
     const int lane = threadIdx.x & 31;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t n32 = round_up(n, 32);
-    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n32; j += stride) {
-        const bool in = (j < n) && (__ldcg(count + j) == 0);  // count is updated by L2 atomics
-        const uint32_t m = __ballot_sync(0xffffffffu, in);
-        if (m) {
-            const int region = (int)(j >> 12);
-            int base = 0;
-            if (lane == 0) base = atomicAdd(cnt + region, __popc(m));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (in) {
-                list[(int64_t)region * kChunkCols + base + __popc(m & ((1u << lane) - 1u))] = (int)j;
-                rank[perm ? perm[j] : j] = r;
-                count[j] = -1;
+    constexpr int kU = 4;  // counts fetched together: one L2 latency for kU positions
+    for (int64_t j0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j0 < n32; j0 += kU * stride) {
+        int v[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const int64_t j = j0 + u * stride;
+            v[u] = (j < n) ? __ldcg(count + j) : -1;  // count is updated by L2 atomics
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const int64_t j = j0 + u * stride;
+            if (j >= n32) break;  // warp-uniform: stride and n32 are multiples of 32
+            const bool in = v[u] == 0;
+            const uint32_t m = __ballot_sync(0xffffffffu, in);
+            if (m) {
+                const int region = (int)(j >> 12);
+                int base = 0;
+                if (lane == 0) base = atomicAdd(cnt + region, __popc(m));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (in) {
+                    list[(int64_t)region * kChunkCols + base + __popc(m & ((1u << lane) - 1u))] = (int)j;
+                    rank[perm ? perm[j] : j] = r;
+                    count[j] = -1;
+                }
             }
         }
     }
