@@ -55,6 +55,33 @@ def make_fitness(n: int, m: int, seed: int = 0) -> np.ndarray:
     return np.random.default_rng(seed).random((n, m), dtype=np.float32)
 
 
+def ncu_traffic_per_launch(kernel_substr: str, n: int, m: int):
+    """DRAM bytes (read + write) per launch of a kernel from the committed ncu launch list of the same
+    workload (profiles/), or None when no capture of this workload is committed."""
+    import csv
+    import glob
+
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", f"launches_*_N{n}_M{m}_v*.csv"))):
+        best = path  # the latest version of the latest round
+    if best is None:
+        return None, None
+    tot, launches = 0.0, 0
+    try:
+        rows = list(csv.reader(l for l in open(best) if l.startswith('"')))
+        h = rows[0]
+        ki, vi, mi = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Name")
+        for r in rows[1:]:
+            if kernel_substr in r[ki]:
+                if r[mi] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    tot += float(r[vi].replace(",", ""))
+                elif r[mi] == "gpu__time_duration.sum":
+                    launches += 1
+    except Exception:
+        return None, None
+    return (tot / launches, os.path.relpath(best, ROOT)) if launches and tot else (None, None)
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -281,11 +308,15 @@ def run_gpu_arm(args, n, m, desc):
     alg_bytes = float(n) * n / 8.0 / world
     real_bytes = alg_bytes * (0.5 + 0.5 * 4096.0 / n) if tri else alg_bytes  # chunks c >= row/4096 only
     roofline = None
+    ncu_bytes, ncu_src = ncu_traffic_per_launch("peel_persistent_kernel", n, m) if world == 1 else (None, None)
     if peel_ms:
         ach = alg_bytes / (peel_ms * 1e-3) / 1e9
         roofline = {"kernel": "peel_persistent_kernel" if world == 1 else "front_subtract_kernel (+ detect/all-gather/expand per front)",
                     "bound": "hbm", "achieved": ach, "peak": hbm_gbs, "unit": "GB/s",
-                    "frac": ach / hbm_gbs, "traffic": real_bytes, "traffic_source": "computed from the triangular layout; ncu dram__bytes in profiles/",
+                    "frac": ach / hbm_gbs, "traffic": ncu_bytes,
+                    "traffic_source": (f"ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, {ncu_src}" if ncu_bytes
+                                       else "no committed ncu capture of this workload"),
+                    "triangle_bytes": real_bytes,
                     "executed_gbs": real_bytes / (peel_ms * 1e-3) / 1e9, "executed_frac": real_bytes / (peel_ms * 1e-3) / 1e9 / hbm_gbs,
                     "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": peel_ms}
     extra = []
