@@ -1,6 +1,7 @@
 // Shared helpers for the evoxb kernels (sm_100a only).
 #pragma once
 
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdint.h>
@@ -93,7 +94,7 @@ inline Profiler &profiler() {
     static thread_local Profiler p;
     return p;
 }
-extern unsigned long long g_launches;  // kernels launched by this library since load (not thread-safe: a statistic)
+extern std::atomic<unsigned long long> g_launches;  // kernels launched by this library since load
 
 // ---- small device helpers ---------------------------------------------------------------------
 __device__ __forceinline__ uint32_t lop3_xor3(uint32_t a, uint32_t b, uint32_t c) {

@@ -19,7 +19,7 @@
 
 namespace evoxb {
 
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 
 struct NcclId {
     char internal[128];  // == ncclUniqueId
@@ -530,7 +530,7 @@ EVOXB_API int evoxb_profile_enable(int on) {
     return 0;
 }
 
-EVOXB_API unsigned long long evoxb_launch_count(void) { return g_launches; }
+EVOXB_API unsigned long long evoxb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 EVOXB_API int evoxb_profile_read(float *ms, const char **names, int cap) {
     Profiler &p = profiler();
