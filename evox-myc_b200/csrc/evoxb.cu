@@ -681,20 +681,15 @@ static int select_impl(int variant, const float *fitness, int64_t n, int m, int6
     if (int rc = launch_crowding(fitness, S.mask, n, m, crowd, S.crowd, s)) return rc;
 
     prof.mark("select_sort", s);
+    // variant 1 only from here on (variant 0 returned above)
     int cur = 0;
-    if (variant == 0) {
-        neg_crowd_keys_kernel<<<gb, 256, 0, s>>>(crowd, n, S.sb.keys[0], S.sb.vals[0]);
-        EVOXB_LAUNCH_CHECK("neg_crowd_keys_kernel");
-        if (int rc = radix_sort_pairs(S.sb, 0, 1, n, nullptr, 0, 32, s, &cur)) return rc;
-    } else {
-        crowd_keys_kernel<<<gb, 256, 0, s>>>(crowd, n, S.sb.keys[0], S.sb.vals[0]);
-        EVOXB_LAUNCH_CHECK("crowd_keys_kernel");
-        if (int rc = radix_sort_pairs(S.sb, 0, 1, n, nullptr, 0, 32, s, &cur)) return rc;  // vals = argsort(crowd)
-        neg_index_keys_kernel<<<gb, 256, 0, s>>>(S.sb.vals[cur], n, S.sb.keys[cur ^ 1], S.sb.vals[cur ^ 1]);
-        EVOXB_LAUNCH_CHECK("neg_index_keys_kernel");
-        cur ^= 1;
-        if (int rc = radix_sort_pairs(S.sb, cur, 1, n, nullptr, 0, round_up(bits_for(n), 8), s, &cur)) return rc;
-    }
+    crowd_keys_kernel<<<gb, 256, 0, s>>>(crowd, n, S.sb.keys[0], S.sb.vals[0]);
+    EVOXB_LAUNCH_CHECK("crowd_keys_kernel");
+    if (int rc = radix_sort_pairs(S.sb, 0, 1, n, nullptr, 0, 32, s, &cur)) return rc;  // vals = argsort(crowd)
+    neg_index_keys_kernel<<<gb, 256, 0, s>>>(S.sb.vals[cur], n, S.sb.keys[cur ^ 1], S.sb.vals[cur ^ 1]);
+    EVOXB_LAUNCH_CHECK("neg_index_keys_kernel");
+    cur ^= 1;
+    if (int rc = radix_sort_pairs(S.sb, cur, 1, n, nullptr, 0, round_up(bits_for(n), 8), s, &cur)) return rc;
     gather_rank_keys_kernel<<<gb, 256, 0, s>>>(rank, S.sb.vals[cur], n, S.sb.keys[cur]);
     EVOXB_LAUNCH_CHECK("gather_rank_keys_kernel");
     if (int rc = radix_sort_pairs(S.sb, cur, 1, n, nullptr, 0, round_up(bits_for(n), 8), s, &cur)) return rc;

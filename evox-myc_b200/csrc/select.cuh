@@ -66,15 +66,6 @@ __global__ void rank_mask_kernel(const int *__restrict__ rank, int64_t n, const 
     if (i < n) mask[i] = rank[i] == __ldcg(worst);
 }
 
-__global__ void neg_crowd_keys_kernel(const float *__restrict__ crowd, int64_t n, uint32_t *__restrict__ keys,
-                                      uint32_t *__restrict__ vals) {
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i < n) {
-        keys[i] = float_to_key(-crowd[i]);
-        vals[i] = (uint32_t)i;
-    }
-}
-
 __global__ void crowd_keys_kernel(const float *__restrict__ x, int64_t n, uint32_t *__restrict__ keys,
                                   uint32_t *__restrict__ vals) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
