@@ -94,6 +94,15 @@ def measured_peaks():
 # --------------------------------------------------------------------------------------------
 # CPU arm: the oracle port on the host cores (bounded sample)
 # --------------------------------------------------------------------------------------------
+def host_cores() -> int:
+    """Host threads the CPU arm uses: every core this process may run on.  Set explicitly on each oracle
+    call, because torchrun exports OMP_NUM_THREADS=1 to its workers and OpenMP would obey it."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:  # pragma: no cover
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_sample_rows(n: int, m: int, budget_s: float) -> int:
     """Largest power-of-two sample size <= n whose estimated oracle time fits the budget."""
     from oracle import c_oracle
@@ -101,7 +110,7 @@ def cpu_sample_rows(n: int, m: int, budget_s: float) -> int:
     probe = min(n, 8192)
     x = make_fitness(probe, m, 123)
     t0 = time.perf_counter()
-    c_oracle.nsga2_select(x, probe // 2)
+    c_oracle.nsga2_select(x, probe // 2, nthreads=host_cores())
     dt = max(time.perf_counter() - t0, 1e-4)
     per_pair = dt / (probe * probe)
     ns = probe
@@ -114,7 +123,7 @@ def cpu_step(x: np.ndarray) -> float:
     from oracle import c_oracle
 
     t0 = time.perf_counter()
-    c_oracle.nsga2_select(x, x.shape[0] // 2)
+    c_oracle.nsga2_select(x, x.shape[0] // 2, nthreads=host_cores())
     return time.perf_counter() - t0
 
 
@@ -124,7 +133,9 @@ def run_reference_arm(args, n, m, desc):
         return  # the CPU arm runs on rank 0 alone
     from oracle import c_oracle
 
-    cores = c_oracle.num_threads()
+    cores = host_cores()
+    # the same sample at every --gpus value: the largest power of two whose step stays within a fixed
+    # per-step budget on this host (threads pinned above, so the choice does not depend on the launcher)
     ns = cpu_sample_rows(n, m, budget_s=max(2.0, 120.0 / (args.steps + args.warmup)))
     x = make_fitness(ns, m, 0)
     for _ in range(args.warmup):
@@ -138,7 +149,7 @@ def run_reference_arm(args, n, m, desc):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "N": n, "M": m, "sample_rows": ns,
+        "config": {"workload": desc, "N": n, "M": m, "sample_rows": ns, "cores": cores,
                    "step": "non_dominated_sort + worst-rank mask + crowding_distance + survivor order (nsga2.py:90-96)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -351,7 +362,7 @@ def run_gpu_arm(args, n, m, desc):
         ns = cpu_sample_rows(n, m, budget_s=20.0)
         xs = make_fitness(ns, m, 0)
         dt = cpu_step(xs)
-        cpu = {"value": ns * ns / dt, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port",
+        cpu = {"value": ns * ns / dt, "unit": UNIT, "cores": host_cores(), "kind": "port",
                "sample": f"{ns} of {n} rows (same distribution, M={m}), one step = {dt:.2f} s"}
 
     line = {

@@ -94,6 +94,18 @@ def uniform_f32(key: tuple[int, int], n: int, minval: np.float32, maxval: np.flo
     return np.maximum(minval, scaled)
 
 
+def uniform_array_f32(seed: int, shape: tuple[int, ...], minval, maxval) -> np.ndarray:
+    """``jax.random.uniform(jax.random.PRNGKey(seed), shape, minval=minval, maxval=maxval)`` in float32,
+    with ``minval`` / ``maxval`` broadcast against ``shape`` (the call of tests/test_lsmop.py:10-14)."""
+    n = int(np.prod(shape))
+    bits = random_bits32(prng_key(seed), n)
+    float_bits = (bits >> np.uint32(9)) | np.float32(1.0).view(np.uint32)
+    floats = (float_bits.view(np.float32) - np.float32(1.0)).reshape(shape)
+    lo = np.broadcast_to(np.asarray(minval, dtype=np.float32), shape)
+    hi = np.broadcast_to(np.asarray(maxval, dtype=np.float32), shape)
+    return np.maximum(lo, (floats * (hi - lo) + lo).astype(np.float32))
+
+
 def normal_f32(seed: int, shape: tuple[int, ...]) -> np.ndarray:
     """``jax.random.normal(jax.random.PRNGKey(seed), shape)`` in float32."""
     n = int(np.prod(shape))

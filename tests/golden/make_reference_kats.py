@@ -53,6 +53,14 @@ out["crowd_front0_128x8_prng314"] = {
     "rtol": 1e-5,
     "dist": vals,
 }
+# tests/test_lsmop.py:10-29: spot values of LSMOP1 on jax.random.uniform(PRNGKey(0), (100, 300), 0, upper)
+out["lsmop1_100x300_prng0"] = {
+    "source": "tests/test_lsmop.py:10-29",
+    "input": "jax.random.uniform(PRNGKey(0), (100, 300), minval=0, maxval=[1, 1, 10 x 298]); LSMOP1(d=300, m=3)",
+    "shape": [100, 3],
+    "spot": [[1, 1, 12.5981], [1, 2, 21.2454]],
+    "atol": 1e-4,
+}
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "reference_kats.json")
 json.dump(out, open(path, "w"), indent=1)
 print("wrote", path, "with", len(vals), "golden distances")

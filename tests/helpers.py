@@ -56,3 +56,16 @@ def chain(n, m):
     """A single dominance chain: n fronts of one member each (deepest possible peel)."""
     v = np.arange(n, dtype=np.float32)[:, None]
     return np.repeat(v, m, axis=1)
+
+
+def lsmop1(n, m=10, d=None, seed=0):
+    """LSMOP1 objectives (reference: problems/numerical/lsmop.py:127-141) of decision vectors uniform in
+    [0, 1]^(m-1) x [0, 10]^(d-m+1), the box of tests/test_lsmop.py:10-14; d = 100 m as the reference's
+    base class defaults to (lsmop.py:40-43)."""
+    from oracle import lsmop_oracle
+
+    d = d or 100 * m
+    rng = np.random.default_rng(seed)
+    x = rng.random((n, d), dtype=np.float32)
+    x[:, m - 1 :] *= np.float32(10)
+    return lsmop_oracle.lsmop1(x, m)

@@ -166,3 +166,46 @@ def test_odd_large_size_many_chunks():
 
     x = h.nasty(150001, 4, 53)
     assert np.array_equal(e.non_dominated_sort(x), c_oracle.non_dominated_sort(x))
+
+
+def test_config5_full_size_lsmop1():
+    """BASELINE config 5 at its own size: N = 65536 (pop 32768), M = 10, LSMOP1 objectives with d = 1000
+    (tests/helpers.lsmop1, restating lsmop.py:127-141).  Ranks bit-exact and the NSGA-III cut-off rank
+    (nsga3.py:96-98) against the C oracle."""
+    import evox_myc_b200 as e
+    from oracle import c_oracle
+
+    n, m = 65536, 10
+    x = h.lsmop1(n, m, seed=54)
+    want = c_oracle.non_dominated_sort(x)
+    rank, last = e.nsga3_last_rank(x, n // 2)
+    assert np.array_equal(rank, want)
+    assert int(last) == int(np.sort(want, kind="stable")[n // 2])
+    p = np.random.default_rng(10).permutation(n)
+    assert np.array_equal(e.non_dominated_sort(x[p]), want[p])
+
+
+def test_config5_shape_uniform_m10():
+    """Same shape on uniform-random fitness (a single huge front plus a thin tail at M = 10)."""
+    from oracle import c_oracle
+
+    x = h.uniform(65536, 10, 55)
+    assert np.array_equal(_gpu_rank(x), c_oracle.non_dominated_sort(x))
+
+
+def test_deep_front_stress_m2_full_size():
+    """SURVEY.md 8(d) deep-front stress: uniform M = 2 at N = 65536 (about 500 fronts): ranks, survivor
+    order and crowding against the C oracle."""
+    import evox_myc_b200 as e
+    from oracle import c_oracle
+
+    n = 65536
+    x = h.uniform(n, 2, 56)
+    order, rank, crowd = e.nsga2_select(x, n // 2, return_details=True)
+    w_order, w_rank, w_crowd = c_oracle.nsga2_select(x, n // 2)
+    assert int(w_rank.max()) > 300
+    assert np.array_equal(rank, w_rank)
+    assert np.array_equal(order, w_order)
+    fin = np.isfinite(w_crowd)
+    assert np.array_equal(np.isfinite(crowd), fin)
+    np.testing.assert_allclose(crowd[fin], w_crowd[fin], rtol=1e-6, atol=0)

@@ -62,3 +62,16 @@ def test_crowding_golden_128x8(kats, name, impl):
     assert np.array_equal(np.isinf(d), np.isinf(gold))
     fin = np.isfinite(gold)
     np.testing.assert_allclose(d[fin], gold[fin], rtol=k["rtol"])
+
+
+def test_lsmop1_spot_values(kats):
+    # tests/test_lsmop.py:10-29: the input is regenerated with oracle/jax_prng.py
+    from oracle import lsmop_oracle
+
+    k = kats["lsmop1_100x300_prng0"]
+    upper = np.hstack([np.ones(2), 10 * np.ones(298)]).astype(np.float32)
+    data = jax_prng.uniform_array_f32(0, (100, 300), 0.0, upper)
+    r = lsmop_oracle.lsmop1(data, 3)
+    assert list(r.shape) == k["shape"]
+    for i, j, v in k["spot"]:
+        assert abs(float(r[i, j]) - v) < k["atol"]
