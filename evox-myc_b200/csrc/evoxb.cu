@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include "dominance.cuh"
 #include "peel.cuh"
+#include "peel_flow.cuh"
 #include "sort.cuh"
 #include "presort.cuh"
 #include "crowding.cuh"
@@ -69,6 +70,7 @@ struct NdsLayout {
     uint32_t *recv_bits;  // [nranks][slice_chunks][128]
     int *totals;          // front sizes of the current batch of fronts
     int *cnt;             // members per region of the current front
+    unsigned char *flow_ring;  // single-GPU exchange buffer of the data-flow peel (peel_flow.cuh)
     size_t bytes;
 };
 
@@ -114,6 +116,7 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         L.totals = c.take<int>(64);
         L.cnt = c.take<int>(kMaxChunks);
     }
+    L.flow_ring = c.take<unsigned char>(flow_ring_bytes(L.npad / 32));
     L.D = c.take<uint32_t>((size_t)n_rows * (size_t)L.row_words);
     L.bytes = c.total();
     return L;
@@ -157,6 +160,145 @@ static int coop_blocks(const void *kern, int threads, int cap_per_sm, int *block
     if (per_sm > cap_per_sm) per_sm = cap_per_sm;
     *blocks = sms * per_sm;
     if (used < 16) cache[used++] = Entry{dev, kern, *blocks};
+    return 0;
+}
+
+}  // namespace evoxb
+
+
+namespace evoxb {
+
+// ---- data-flow peel (peel_flow.cuh): launch configuration ------------------------------------------
+// Which peel runs: "flow" = peel_flow_kernel wherever it is applicable, "grid" = the cooperative-grid
+// kernels of peel.cuh, unset = by population size (see peel_use_flow).  Experiment knob, read once.
+static int peel_mode_env() {
+    static const int mode = [] {
+        const char *ev = getenv("EVOXB_PEEL_MODE");
+        if (!ev) return 0;
+        if (!strcmp(ev, "flow")) return 1;
+        if (!strcmp(ev, "grid")) return 2;
+        return 0;
+    }();
+    return mode;
+}
+
+// Default choice between the two peel kernels on one GPU (measured on the B200).
+static bool peel_use_flow(int64_t n, int m) {
+    if (m <= 3) return n <= 131072;
+    if (m == 4) return n <= 65536;
+    return n <= 32768;
+}
+
+struct FlowLaunch {
+    FlowPlan plan;
+    size_t smem;
+    bool ok;
+};
+
+constexpr size_t kFlowSmemLimit = 200 * 1024;
+
+// Picks two CTAs per SM when they fit, else one; the plan (column ownership) depends on that choice.
+// Cached per (thread, device, shape): the plan walks every piece on the host.
+static int flow_prepare(int nchunks, ChunkMap cm, bool tri, int count_planes, FlowLaunch *out) {
+    struct Entry { int dev, nchunks, first, stride, nlocal, tri, cp; FlowLaunch fl; };
+    static thread_local Entry cache[8];
+    static thread_local int used = 0, next = 0;
+    int dev = 0;
+    EVOXB_CUDA(cudaGetDevice(&dev));
+    for (int i = 0; i < used; ++i) {
+        const Entry &e = cache[i];
+        if (e.dev == dev && e.nchunks == nchunks && e.first == cm.first && e.stride == cm.stride && e.nlocal == cm.nlocal &&
+            e.tri == (int)tri && e.cp == count_planes) {
+            *out = e.fl;
+            return 0;
+        }
+    }
+    FlowLaunch fl{};
+    fl.ok = false;
+    if (nchunks <= kFlowMaxChunks && cm.nlocal >= 1 && count_planes <= kFlowMaxCountPlanes) {
+        static std::mutex mu;
+        static bool attr_set[64] = {};
+        if (dev >= 0 && dev < 64) {
+            std::lock_guard<std::mutex> lock(mu);
+            if (!attr_set[dev]) {
+                EVOXB_CUDA(cudaFuncSetAttribute(peel_flow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFlowSmemLimit));
+                attr_set[dev] = true;
+            }
+        }
+        int sms = 0;
+        EVOXB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        for (int per_sm = 1; per_sm >= 1 && !fl.ok; --per_sm) {
+            FlowPlan plan = flow_make_plan(nchunks, cm, tri, sms * per_sm);
+            if (plan.grid < 1 || plan.max_pieces > kFlowMaxPieces) continue;
+            const size_t smem = flow_smem_bytes(nchunks, count_planes, plan.max_words);
+            if (smem > kFlowSmemLimit) continue;
+            int occ = 0;
+            EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, peel_flow_kernel, kFlowThreads, smem));
+            if (occ < per_sm) continue;
+            fl.plan = plan;
+            fl.smem = smem;
+            fl.ok = true;
+        }
+    }
+    Entry ne{dev, nchunks, cm.first, cm.stride, cm.nlocal, (int)tri, count_planes, fl};
+    if (used < 8) cache[used++] = ne;
+    else { cache[next] = ne; next = (next + 1) % 8; }
+    *out = fl;
+    return 0;
+}
+
+// Development builds only (-DEVOXB_FLOW_TIMING=1): a device buffer the kernel's CTA 0 writes its per-phase
+// clock totals to; printed by scripts/dev_flow_timing.py through evoxb_flow_timing_read.
+static long long *flow_timing_buffer() {
+#if EVOXB_FLOW_TIMING
+    static long long *buf = nullptr;
+    if (!buf) cudaMalloc((void **)&buf, sizeof(long long) * (192 * 8 + 8));
+    return buf;
+#else
+    return nullptr;
+#endif
+}
+
+// Data-flow peel on one GPU: ranks by (sorted) position into L.list, then back through the permutation.
+static int run_peel_flow(const NdsLayout &L, int64_t n, int32_t *rank, const int *perm, const FlowLaunch &fl, int front0_limit,
+                         cudaStream_t s) {
+    FlowArgs a{};
+    a.D = L.D;
+    a.row_words = L.row_words;
+    a.nchunks = L.nchunks;
+    a.n = (int)n;
+    a.tri = L.tri ? 1 : 0;
+    a.cm = ChunkMap{0, 1, L.nchunks};
+    a.count = L.count;
+    a.rank_sorted = perm ? L.list : rank;
+    a.tb = TileBands{L.tri ? L.tile_min1 : nullptr, L.tri ? L.tile_max1 : nullptr};
+    a.peers.base[0] = L.flow_ring;
+    a.me = 0;
+    a.nranks = 1;
+    a.grids[0] = fl.plan.grid;
+    a.slot_words = L.npad / 32;
+    a.count_planes = bits_for(n > 1 ? n : 2);
+    a.max_words = fl.plan.max_words;
+    a.target = fl.plan.target;
+    a.fronts_done = &L.ctrl->fronts_done;
+    a.host_error = nullptr;
+    a.timeout_ns = 4000000000ull;
+    a.timing = flow_timing_buffer();
+    a.front0 = front0_limit >= 0 ? &L.ctrl->front0 : nullptr;
+    a.front0_limit = front0_limit;
+    if (front0_limit >= 0) {
+        front0_size_kernel<<<(unsigned)div_up(n, 256 * 8), 256, 0, s>>>(L.count, (int)n, &L.ctrl->front0);
+        EVOXB_LAUNCH_CHECK("front0_size_kernel");
+    }
+    EVOXB_CUDA(cudaMemsetAsync(L.flow_ring, 0, flow_ring_bytes(L.npad / 32), s));
+    void *args[] = {&a};
+    EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_flow_kernel, dim3(fl.plan.grid), dim3(kFlowThreads), args, fl.smem, s));
+    ++g_launches;
+    if (perm) {
+        unpermute_rank_kernel<<<(unsigned)(L.npad / 256), 256, 0, s>>>(L.list, perm, (int)L.npad, &L.ctrl->fronts_done, a.front0,
+                                                                       front0_limit, rank);
+        EVOXB_LAUNCH_CHECK("unpermute_rank_kernel");
+    }
     return 0;
 }
 
@@ -232,6 +374,22 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     EVOXB_LAUNCH_CHECK("dominator_count_kernel");
 
     prof.mark("peel", s);
+    // Which kernel peels: the data-flow kernel wins where fronts are many and small (its per-front cost is a
+    // few microseconds instead of ~16), the grid-wide kernel where they are few and huge (bandwidth).  The
+    // number of fronts is not known in advance, so for populations in the data-flow kernel's range BOTH are
+    // enqueued and the size of front 0 decides on the device which one returns at once (no host round trip).
+    FlowLaunch fl{};
+    if (peel_mode_env() != 2) {
+        if (int rc = flow_prepare(L.nchunks, ChunkMap{0, 1, L.nchunks}, L.tri, bits_for(n > 1 ? n : 2), &fl)) return rc;
+    }
+    int front0_limit = -1;  // -1: only the grid-wide kernel runs
+    if (fl.ok) {
+        if (peel_mode_env() == 1) return run_peel_flow(L, n, rank, perm, fl, -1, s);
+        if (peel_use_flow(n, m)) {
+            front0_limit = (int)(n / 16);
+            if (int rc = run_peel_flow(L, n, rank, perm, fl, front0_limit, s)) return rc;
+        }
+    }
     {
         const uint32_t *D = L.D;
         int64_t row_words = L.row_words;
@@ -243,7 +401,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         int *list = L.list;
         PeelCtrl *ctrl = L.ctrl;
         TileBands tbv = tb;
-        void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl, &tbv};
+        void *args[] = {&D, &row_words, &nchunks, &nn, &tri_arg, &count, &rk, &perm, &list, &ctrl, &tbv, &front0_limit};
         EVOXB_CUDA(cudaLaunchCooperativeKernel(peel_kern, dim3(peel_blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
     }
@@ -529,6 +687,13 @@ EVOXB_API int evoxb_profile_enable(int on) {
     profiler().enabled = on != 0;
     return 0;
 }
+
+#if EVOXB_FLOW_TIMING
+EVOXB_API int evoxb_flow_timing_read(long long *out) {  // out[192 * 8 + 8]
+    cudaDeviceSynchronize();
+    return cudaMemcpy(out, flow_timing_buffer(), sizeof(long long) * (192 * 8 + 8), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -3;
+}
+#endif
 
 EVOXB_API unsigned long long evoxb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 

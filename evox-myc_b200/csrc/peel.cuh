@@ -385,6 +385,7 @@ __device__ void collect_front(int *__restrict__ count, int n, int r, int *__rest
 struct PeelCtrl {
     int cnt[2][kMaxChunks];  // members per region of the current / next front (double-buffered)
     int fronts_done;         // number of fronts peeled (written at exit)
+    int front0;              // size of front 0 (front0_size_kernel); only set when both peel kernels are enqueued
 };
 
 // K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).
@@ -392,10 +393,13 @@ template <int kPer>
 __global__ void __launch_bounds__(kPeelThreads, 2)
 peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri,
                        int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm,
-                       int *__restrict__ list, PeelCtrl *__restrict__ ctrl, TileBands tb) {
+                       int *__restrict__ list, PeelCtrl *__restrict__ ctrl, TileBands tb, int front0_limit) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     cg::grid_group grid = cg::this_grid();
+    // front0_limit >= 0: the data-flow kernel (peel_flow.cuh) was enqueued in front of this one and did the work
+    // unless front 0 is larger than the limit (uniform over the grid, before any grid-wide sync)
+    if (front0_limit >= 0 && __ldcg(&ctrl->front0) <= front0_limit) return;
     const ChunkMap cm{0, 1, nchunks};
     int r = 0;
     for (;;) {
