@@ -34,10 +34,14 @@ EXPORTS = [
     "evoxb_gather_rows_f32",
     "evoxb_sbx_pm_clip_f32",
     "evoxb_dtlz2_f32",
+    "evoxb_lsmop1_f32",
     "evoxb_comm_unique_id",
     "evoxb_comm_create",
     "evoxb_comm_destroy",
     "evoxb_comm_status",
+    "evoxb_comm_poll_error",
+    "evoxb_comm_set_timeout_ms",
+    "evoxb_comm_last_path",
     "evoxb_shard_plan",
     "evoxb_nds_sharded_workspace_bytes",
     "evoxb_nds_rank_sharded_f32",
@@ -83,11 +87,15 @@ def lib() -> ctypes.CDLL:
         f32, u32 = ctypes.c_float, ctypes.c_uint32
         L.evoxb_sbx_pm_clip_f32.argtypes = [vp, i64, i32, vp, vp, f32, f32, f32, f32, u32, u32, vp, vp]
         L.evoxb_dtlz2_f32.argtypes = [vp, i64, i32, i32, vp, vp]
+        L.evoxb_lsmop1_f32.argtypes = [vp, i64, i32, i32, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32), vp, vp]
         ip = ctypes.POINTER(ctypes.c_int)
         L.evoxb_comm_unique_id.argtypes = [vp]
         L.evoxb_comm_create.argtypes = [ctypes.c_char_p, i32, i32, ctypes.POINTER(vp)]
         L.evoxb_comm_destroy.argtypes = [vp]
         L.evoxb_comm_status.argtypes = [vp, ip, ip, ip]
+        L.evoxb_comm_poll_error.argtypes = [vp]
+        L.evoxb_comm_set_timeout_ms.argtypes = [vp, i64]
+        L.evoxb_comm_last_path.argtypes = [vp]
         L.evoxb_shard_plan.argtypes = [i64, i32, i32, ip, ip, ip, ip]
         L.evoxb_nds_sharded_workspace_bytes.argtypes = [i64, i32, i32, i32, ctypes.POINTER(sz)]
         L.evoxb_nds_rank_sharded_f32.argtypes = [vp, i64, i32, vp, vp, sz, vp, vp]

@@ -39,6 +39,10 @@ struct evoxb_comm {
     unsigned char *peer_ptr[16] = {};     // peers' exchange buffers mapped into this process
     unsigned char **peers_dev = nullptr;  // the same pointers in device memory, for the kernel
     int *fronts_dev = nullptr;            // fronts peeled by the last call (device int)
+    size_t flow_off = 0;                  // offset of the data-flow kernel's exchange region inside every xbuf
+    unsigned int *h_err = nullptr;        // pinned, mapped host word the kernels raise on a peer time-out (sticky)
+    unsigned long long timeout_ns = 4000000000ull;  // how long a kernel waits for a peer before it gives up
+    int last_path = 0;                    // which exchange the last call used: 0 NCCL all-gather, 1 grid-wide peer kernel, 2 data-flow kernel
 };
 
 namespace evoxb {
@@ -449,12 +453,30 @@ static NcclApi &nccl_api() {
                                  nccl_api().GetErrorString(r__));                                   \
     } while (0)
 
+// Which fused kernel peels across GPUs.  The data-flow kernel needs every rank to own at least one chunk (a
+// rank without columns would publish nothing, and nobody would wait for it to have read a buffer before it is
+// reused).  It wins where a front is little work per GPU (latency: many GPUs or a small population); the
+// grid-wide kernel keeps the cases with megabytes per front and GPU.  Must be the same on every rank.
+static bool sharded_use_flow(int64_t n, int m, int nchunks, int nranks) {
+    (void)m;
+    if (nchunks < nranks || nchunks > kFlowMaxChunks) return false;
+    static const int mode = [] {
+        const char *ev = getenv("EVOXB_PEEL_MODE");
+        return !ev ? 0 : !strcmp(ev, "flow") ? 1 : !strcmp(ev, "grid") ? 2 : 0;
+    }();
+    if (mode) return mode == 1;
+    return n / nranks <= 32768;
+}
+
 // Row-sharded^T ranking: every GPU presorts (same permutation everywhere), builds and keeps the
 // matrix columns of its own chunks for ALL rows, and owns count[] of those columns.  Per front the
 // GPUs exchange one bit per individual (ncclAllGather of N/8 bytes in total); no other traffic.
 // The host checks "front empty?" once per kFrontBatch fronts (one 4-byte-per-front D2H + stream sync).
 static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank, const NdsLayout &L, evoxb_comm *comm,
                            cudaStream_t s, Profiler &prof) {
+    if (comm->h_err && *reinterpret_cast<volatile unsigned int *>(comm->h_err))
+        return fail(EVOXB_E_NCCL, "an earlier call on this communicator gave up waiting for a peer GPU (its ranks are -1); "
+                                  "the communicator cannot be used any more: destroy it and create a new one on every rank");
     if (!L.tri) return fail(EVOXB_E_UNSUPPORTED, "the multi-GPU path supports m <= 16 (got %d)", m);
     if (L.nchunks > kMaxChunks)
         return fail(EVOXB_E_UNSUPPORTED, "n = %lld exceeds %d rows", (long long)n, kMaxChunks * kChunkCols);
@@ -480,7 +502,56 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
 
     prof.mark("peel", s);
     const size_t slice_words = (size_t)L.slice_chunks * kChunkWords;
+    if (comm->p2p && sharded_use_flow(n, m, L.nchunks, L.nranks)) {
+        // data-flow peel across the GPUs: the same kernel as on one GPU, its tagged words and flags also stored
+        // into every peer's exchange region over NVLink (peel_flow.cuh)
+        FlowArgs a{};
+        bool all_ok = true;
+        FlowLaunch mine{};
+        for (int q = 0; q < L.nranks && all_ok; ++q) {
+            const ChunkMap cq{q, L.nranks, q < L.nchunks ? (L.nchunks - q + L.nranks - 1) / L.nranks : 0};
+            FlowLaunch fq{};
+            if (int rc = flow_prepare(L.nchunks, cq, true, bits_for(n > 1 ? n : 2), &fq)) return rc;
+            all_ok = all_ok && fq.ok;
+            a.grids[q] = fq.plan.grid;
+            if (q == comm->rank) mine = fq;
+        }
+        if (all_ok) {
+            a.D = L.D;
+            a.row_words = L.row_words;
+            a.nchunks = L.nchunks;
+            a.n = (int)n;
+            a.tri = 1;
+            a.cm = L.cm;
+            a.count = L.count;
+            a.rank_sorted = L.list;
+            a.tb = tb;
+            for (int q = 0; q < L.nranks; ++q) a.peers.base[q] = comm->peer_ptr[q] + comm->flow_off;
+            a.me = comm->rank;
+            a.nranks = L.nranks;
+            a.slot_words = (int64_t)kFlowMaxChunks * kChunkWords;
+            a.count_planes = bits_for(n > 1 ? n : 2);
+            a.max_words = mine.plan.max_words;
+            a.target = mine.plan.target;
+            a.fronts_done = comm->fronts_dev;
+            a.host_error = comm->h_err;
+            a.timeout_ns = comm->timeout_ns;
+            a.timing = nullptr;
+            a.front0 = nullptr;
+            a.front0_limit = -1;
+            void *args[] = {&a};
+            EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)peel_flow_kernel, dim3(mine.plan.grid), dim3(kFlowThreads), args,
+                                                   mine.smem, s));
+            ++g_launches;
+            unpermute_rank_kernel<<<(unsigned)(L.npad / 256), 256, 0, s>>>(L.list, L.perm, (int)L.npad, comm->fronts_dev, nullptr, -1,
+                                                                           rank);
+            EVOXB_LAUNCH_CHECK("unpermute_rank_kernel");
+            comm->last_path = 2;
+            return 0;
+        }
+    }
     if (comm->p2p && (size_t)L.nranks * slice_words <= (size_t)kXchgSliceWordsCap) {
+        comm->last_path = 1;
         // fused path: one persistent kernel per GPU exchanges the front bitmask over peer memory
         const uint32_t *D = L.D;
         int64_t row_words = L.row_words;
@@ -490,15 +561,20 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         const int *perm = L.perm;
         XchgCtx x{comm->peers_dev, comm->rank, comm->nranks, L.slice_chunks};
         TileBands tbv = tb;
-        void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &x, &fronts, &tbv};
+        unsigned int *herr = comm->h_err;
+        unsigned long long tmo = comm->timeout_ns;
+        void *args[] = {&D, &row_words, &nchunks, &nn, &cm, &count, &rk, &perm, &list, &cnt, &x, &fronts, &tbv, &herr, &tmo};
         // across GPUs every rank still streams all n member rows and the extra CTAs also widen the
         // exchange, so the full grid wins there (measured at 4 and 8 GPUs: 0.93 / 0.83 ms against
         // 1.13 / 0.96 ms with one CTA per SM)
         const int p2p_blocks = L.nranks > 1 ? blocks : peel_grid_for(n, blocks);
         EVOXB_CUDA(cudaLaunchCooperativeKernel(p2p_kern, dim3(p2p_blocks), dim3(kPeelThreads), args, 0, s));
         ++g_launches;
+        poison_ranks_kernel<<<(unsigned)div_up(n, 256), 256, 0, s>>>(rank, (int)n, comm->fronts_dev);  // -1 everywhere after a time-out
+        EVOXB_LAUNCH_CHECK("poison_ranks_kernel");
         return 0;
     }
+    comm->last_path = 0;
     const unsigned detect_blocks = (unsigned)div_up((int64_t)(L.cm.nlocal > 0 ? L.cm.nlocal : 1) * kChunkWords * 32, 256);
     int r = 0;
     for (;;) {
@@ -544,8 +620,10 @@ static void setup_peer_exchange(evoxb_comm *c) {
     static_assert(sizeof(Slot) == 128, "slot size");
     Slot mine{};
     std::vector<Slot> all((size_t)P);
-    ok = ok && cudaMalloc((void **)&c->xbuf, xchg_buffer_bytes()) == cudaSuccess;
-    ok = ok && cudaMemset(c->xbuf, 0, xchg_buffer_bytes()) == cudaSuccess;
+    c->flow_off = (xchg_buffer_bytes() + 255) & ~(size_t)255;
+    const size_t xbytes = c->flow_off + flow_ring_bytes((int64_t)kFlowMaxChunks * kChunkWords);
+    ok = ok && cudaMalloc((void **)&c->xbuf, xbytes) == cudaSuccess;
+    ok = ok && cudaMemset(c->xbuf, 0, xbytes) == cudaSuccess;
     ok = ok && cudaMalloc((void **)&c->fronts_dev, sizeof(int)) == cudaSuccess;
     ok = ok && cudaMalloc((void **)&c->peers_dev, sizeof(unsigned char *) * kXchgMaxRanks) == cudaSuccess;
     ok = ok && cudaMalloc((void **)&hbuf_dev, sizeof(Slot) * (size_t)(P + 1)) == cudaSuccess;
@@ -905,6 +983,8 @@ EVOXB_API int evoxb_comm_create(const void *id128, int rank, int nranks, evoxb_c
         delete c;
         return fail(EVOXB_E_CUDA, "cudaHostAlloc failed: %s", cudaGetErrorString(e));
     }
+    c->h_err = reinterpret_cast<unsigned int *>(c->h_flags + 32);
+    *c->h_err = 0u;
     setup_peer_exchange(c);  // best effort: c->p2p says whether the fused path is available
     *out = c;
     return 0;
@@ -917,12 +997,27 @@ EVOXB_API int evoxb_comm_status(evoxb_comm *comm, int *p2p_enabled, int *error, 
     if (fronts) *fronts = 0;
     if (comm->p2p) {
         XchgHeader h;
+        FlowHeader fh;
         EVOXB_CUDA(cudaMemcpy(&h, comm->xbuf, sizeof(h), cudaMemcpyDeviceToHost));
-        if (error) *error = (int)h.error;
+        EVOXB_CUDA(cudaMemcpy(&fh, comm->xbuf + comm->flow_off, sizeof(fh), cudaMemcpyDeviceToHost));
+        if (error) *error = (h.error || fh.error || (comm->h_err && *comm->h_err)) ? 1 : 0;
         if (fronts) EVOXB_CUDA(cudaMemcpy(fronts, comm->fronts_dev, sizeof(int), cudaMemcpyDeviceToHost));
     }
     return 0;
 }
+
+EVOXB_API int evoxb_comm_poll_error(evoxb_comm *comm) {
+    return (comm && comm->h_err && *reinterpret_cast<volatile unsigned int *>(comm->h_err)) ? 1 : 0;
+}
+
+EVOXB_API int evoxb_comm_set_timeout_ms(evoxb_comm *comm, int64_t ms) {
+    if (!comm) return fail(EVOXB_E_INVALID, "comm is null");
+    if (ms < 1) return fail(EVOXB_E_INVALID, "time-out must be at least 1 ms (got %lld)", (long long)ms);
+    comm->timeout_ns = (unsigned long long)ms * 1000000ull;
+    return 0;
+}
+
+EVOXB_API int evoxb_comm_last_path(evoxb_comm *comm) { return comm ? comm->last_path : -1; }
 
 EVOXB_API int evoxb_comm_destroy(evoxb_comm *comm) {
     if (!comm) return 0;
@@ -1002,6 +1097,25 @@ EVOXB_API int evoxb_dtlz2_f32(const float *x, int64_t n, int d, int m, float *f,
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     dtlz2_kernel<<<(unsigned)div_up(n, 128), 128, 0, s>>>(x, n, d, m, f);
     EVOXB_LAUNCH_CHECK("dtlz2_kernel");
+    return 0;
+}
+
+EVOXB_API int evoxb_lsmop1_f32(const float *x, int64_t n, int d, int m, const int32_t *sublen, const int32_t *start, float *f,
+                               evoxb_stream_t stream) {
+    if (n < 0 || m < 2 || m > EVOXB_MAX_OBJECTIVES || d < m)
+        return fail(EVOXB_E_INVALID, "bad shape (n=%lld, d=%d, m=%d; 2 <= m <= %d <= d)", (long long)n, d, m, EVOXB_MAX_OBJECTIVES);
+    if (n == 0) return 0;
+    if (!x || !f || !sublen || !start) return fail(EVOXB_E_INVALID, "null pointer");
+    LsmopGroups gr{};
+    for (int i = 0; i < m; ++i) {
+        gr.sublen[i] = sublen[i];
+        gr.start[i] = start[i];
+        if (sublen[i] < 0 || start[i] < 0 || (int64_t)start[i] + m - 1 + (int64_t)kLsmopNk * sublen[i] > d)
+            return fail(EVOXB_E_INVALID, "group %d (start %d, sublen %d) does not fit d = %d", i, start[i], sublen[i], d);
+    }
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    lsmop1_kernel<<<(unsigned)div_up(n * 32, 256), 256, 0, s>>>(x, n, d, m, gr, f);
+    EVOXB_LAUNCH_CHECK("lsmop1_kernel");
     return 0;
 }
 

@@ -544,7 +544,7 @@ __global__ void __launch_bounds__(kPeelThreads, 2)
 peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, ChunkMap cm,
                 int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm, int *__restrict__ list,
                 int *__restrict__ cnt, XchgCtx x, int *__restrict__ fronts_done,
-                TileBands tb) {
+                TileBands tb, unsigned int *host_error, unsigned long long timeout_ns) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     __shared__ int sh_wsum[kPeelThreads / 32];
@@ -594,7 +594,7 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
                 if ((++spins & 1023u) == 0u) {
                     const unsigned long long now = global_ns();
                     if (t0 == 0ull) t0 = now;
-                    if (now - t0 > 4000000000ull || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
+                    if (now - t0 > timeout_ns || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
                         sh_fail = 1;
                         break;
                     }
@@ -616,7 +616,7 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
                         if ((++spins & 1023u) == 0u) {
                             const unsigned long long now = global_ns();
                             if (t0 == 0ull) t0 = now;
-                            if (now - t0 > 4000000000ull || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
+                            if (now - t0 > timeout_ns || *reinterpret_cast<volatile unsigned int *>(&hdr->error)) {
                                 sh_fail = 1;
                                 break;
                             }
@@ -650,7 +650,13 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
             }
         }
         if (sh_fail) {  // a peer never delivered: flag it (all CTAs see hdr->error and leave too)
-            if (threadIdx.x == 0) hdr->error = 1;
+            if (threadIdx.x == 0) {
+                hdr->error = 1;
+                if (host_error) {  // mapped host word: the library refuses further calls on this communicator
+                    *host_error = 1u;
+                    __threadfence_system();
+                }
+            }
             failed = true;
         }
         grid.sync();
@@ -669,6 +675,14 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
         if (!failed) hdr->epoch = e;
         *fronts_done = failed ? -1 : r;
     }
+}
+
+// After a peer time-out (fronts_done < 0) the ranks written so far are meaningless: make that visible.
+__global__ void __launch_bounds__(256)
+poison_ranks_kernel(int *__restrict__ rank, int n, const int *__restrict__ fronts_done) {
+    if (*fronts_done >= 0) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) rank[i] = -1;
 }
 
 }  // namespace evoxb

@@ -319,30 +319,34 @@ __device__ __forceinline__ void flow_piece_pass(const FlowArgs &a, const FlowPie
         uint32_t pl[kFlowRowPlanes];
 #pragma unroll
         for (int p = 0; p < kFlowRowPlanes; ++p) pl[p] = 0u;
+        // Tiles of kFlowTileWords: every thread owns up to U 16-byte slots of a tile (tile == U * 512 slots).  The
+        // loads of tile k + 1 are issued before tile k is added, so DRAM latency overlaps the adds.
+        constexpr int U = kFlowTileWords / 4 / kFlowThreads;  // 4
+        uint4 v[U];
+        auto issue = [&](int qb) {
+            const int items = min(rows_per_tile, nm - qb) << lg_parts;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = t + u * kFlowThreads;
+                const int row = sm.rows[qb + (min(i, items - 1) >> lg_parts)];
+                // rows of later chunks have nothing (and nothing defined) in this chunk's columns; a row tile whose
+                // smallest x_1 exceeds the column tile's largest was zero-filled by the build kernel
+                const bool fetch = i < items && (!tri || (row >> 12) <= pc.chunk) && !(sm.tmin[row >> 10] > col_max);
+                v[u] = ldg_stream_v4_if(base + (int64_t)row * row_vec, fetch);
+            }
+        };
+        issue(0);
 #pragma unroll 1
         for (int qb = 0; qb < nm; qb += rows_per_tile) {
             const int nt = min(rows_per_tile, nm - qb);
             const int items = nt << lg_parts;
-            constexpr int U = 4;
-#pragma unroll 1
-            for (int i0 = t; i0 < items; i0 += kFlowThreads * U) {
-                uint4 v[U];
 #pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int i = i0 + u * kFlowThreads;
-                    const int row = sm.rows[qb + (min(i, items - 1) >> lg_parts)];
-                    // rows of later chunks have nothing (and nothing defined) in this chunk's columns; a row tile
-                    // whose smallest x_1 exceeds the column tile's largest was zero-filled by the build kernel
-                    const bool fetch = i < items && (!tri || (row >> 12) <= pc.chunk) && !(sm.tmin[row >> 10] > col_max);
-                    v[u] = ldg_stream_v4_if(base + (int64_t)row * row_vec, fetch);
-                }
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int i = i0 + u * kFlowThreads;
-                    if (i < items) tile4[i] = v[u];
-                }
+            for (int u = 0; u < U; ++u) {
+                const int i = t + u * kFlowThreads;
+                if (i < items) tile4[i] = v[u];
             }
             __syncthreads();
+            if (qb + rows_per_tile < nm) issue(qb + rows_per_tile);
             FLOW_T(5)
             if (g < ng) {
 #pragma unroll 1

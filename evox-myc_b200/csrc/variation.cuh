@@ -113,4 +113,47 @@ __global__ void dtlz2_kernel(const float *__restrict__ x, int64_t n, int d, int 
     }
 }
 
+// LSMOP1 (lsmop.py:127-141): linear linkage x'_j = (1 + (j + 1) / d) x_j - 10 x_0 for j >= m - 1, then for
+// objective i the sphere function over its nk = 5 consecutive sub-blocks (lsmop.py:88-111; the blocks of a
+// group are adjacent, so a group is one run of nk * sublen[i] variables starting at start[i] + m - 1),
+// g_i = sum / sublen[i] / nk, f_k = (1 + g_k) * prod_{t < m-1-k} x_t * (k > 0 ? 1 - x_{m-1-k} : 1).
+// One warp per row (a row is d floats, 4 KB at d = 1000): lanes stride over a group, shuffle-reduce per group.
+constexpr int kLsmopNk = 5;
+struct LsmopGroups {
+    int sublen[EVOXB_MAX_OBJECTIVES];  // variables per sub-block of objective i
+    int start[EVOXB_MAX_OBJECTIVES];   // lsmop.py:52 `len[i]` (offset of the group among the distance variables)
+};
+
+__global__ void __launch_bounds__(256)
+lsmop1_kernel(const float *__restrict__ x, int64_t n, int d, int m, LsmopGroups gr, float *__restrict__ f) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (row >= n) return;  // warp-uniform
+    const float *xi = x + row * d;
+    const float x0_10 = xi[0] * 10.0f;
+    const float inv_d = (float)d;
+    float g_mine = 0.0f;  // lane i keeps g_i
+    for (int i = 0; i < m; ++i) {
+        const int first = gr.start[i] + m - 1, len = kLsmopNk * gr.sublen[i];
+        float acc = 0.0f;
+        for (int j = first + lane; j < first + len; j += 32) {
+            const float scale = 1.0f + (float)(j + 1) / inv_d;
+            const float v = scale * xi[j] - x0_10;
+            acc += v * v;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        const float g = acc / (float)gr.sublen[i] / (float)kLsmopNk;
+        if (lane == i) g_mine = g;
+    }
+    // lane k writes objective k: cumulative product of the first m - 1 - k position variables
+    if (lane < m) {
+        const int k = lane;
+        float cp = 1.0f;
+        for (int t = 0; t < m - 1 - k; ++t) cp *= xi[t];
+        const float tail = (k > 0) ? 1.0f - xi[m - 1 - k] : 1.0f;
+        f[row * m + k] = (1.0f + g_mine) * cp * tail;
+    }
+}
+
 }  // namespace evoxb

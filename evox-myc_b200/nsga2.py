@@ -84,6 +84,46 @@ class DTLZ2:
         return f, state
 
 
+class LSMOP1:
+    """LSMOP1 -- problems/numerical/lsmop.py:17-58 (group sizes) and :114-141 (``evaluate``).
+
+    ``d`` defaults as in the reference: the base class sizes the groups for ``d = 100 m`` (lsmop.py:40-43), then
+    ``LSMOP1.__init__`` resets ``self.d = m + 4`` when no ``d`` is given (:122-125) -- the groups keep the sizes
+    computed from 100 m.  Pass ``d`` explicitly (as the reference's own test does, tests/test_lsmop.py:19-20).
+    """
+
+    NK = 5
+
+    def __init__(self, d=None, m=None, ref_num=1000):
+        import numpy as np
+
+        self.m = 3 if m is None else m
+        group_d = self.m * 100 if d is None else d
+        self.d = self.m + 4 if d is None else d
+        self.ref_num = ref_num
+        c = [3.8 * 0.1 * (1 - 0.1)]
+        for _ in range(1, self.m):
+            c.append(3.8 * c[-1] * (1 - c[-1]))
+        c = np.asarray(c, dtype=np.float32)  # the reference evaluates these lines in float32 (jnp arrays)
+        sublen = np.floor(c / np.sum(c, dtype=np.float32) * np.float32(group_d) / np.float32(self.NK)).astype(np.float32)
+        length = np.concatenate([[0], np.cumsum(sublen * self.NK)])
+        self.sublen = tuple(int(v) for v in sublen)
+        self.len = tuple(int(v) for v in length)
+
+    def evaluate(self, state, X: torch.Tensor):
+        import ctypes
+
+        L = _lib.lib()
+        X = X.to(torch.float32).contiguous()
+        n, d = X.shape
+        f = torch.empty((n, self.m), dtype=torch.float32, device=X.device)
+        sub = (ctypes.c_int32 * self.m)(*self.sublen)
+        start = (ctypes.c_int32 * self.m)(*self.len[: self.m])
+        with torch.cuda.device(X.device):
+            _lib.check(L.evoxb_lsmop1_f32(X.data_ptr(), n, d, self.m, sub, start, f.data_ptr(), rt.stream_ptr(X.device)))
+        return f, state
+
+
 class NSGA2:
     """NSGA-II -- src/evox/algorithms/mo/nsga2.py:22-100."""
 

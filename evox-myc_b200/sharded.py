@@ -112,6 +112,25 @@ class ShardedSelector:
             _lib.check(_lib.lib().evoxb_comm_status(self._comm, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
         return bool(a.value), bool(b.value), c.value
 
+    PATHS = {0: "ncclAllGather per front", 1: "grid-wide peer-memory kernel", 2: "data-flow peer-memory kernel"}
+
+    def last_path(self) -> str:
+        """Which exchange the last call used (see include/evoxb.h, section e)."""
+        return self.PATHS.get(int(_lib.lib().evoxb_comm_last_path(self._comm)), "unknown")
+
+    def set_timeout_ms(self, ms: int) -> None:
+        _lib.check(_lib.lib().evoxb_comm_set_timeout_ms(self._comm, int(ms)))
+
+    def _raise_if_peer_failed(self, synced: bool) -> None:
+        """A peer time-out leaves ranks of -1; that must be an exception, not a value somebody has to inspect.
+        The kernels raise a host word, so after the call's stream has been synchronised this is exact; for
+        results left on the device the check covers every EARLIER call (the library itself refuses further
+        calls on a failed communicator)."""
+        if _lib.lib().evoxb_comm_poll_error(self._comm):
+            raise _lib.EvoxbError(-5, "a peer GPU did not answer within the time-out: the ranks of that call are -1 "
+                                      "and this ShardedSelector is unusable (close it on every rank and make a new one)"
+                                      + ("" if synced else " [detected on a later call]"))
+
     def close(self):
         if getattr(self, "_comm", None):
             _lib.lib().evoxb_comm_destroy(self._comm)
@@ -132,7 +151,9 @@ class ShardedSelector:
         with torch.cuda.device(self.device):
             _lib.check(L.evoxb_nds_rank_sharded_f32(a.dev.data_ptr(), n, m, rank.data_ptr(), self._ws.data_ptr(),
                                                     self._ws.numel(), self._comm, rt.stream_ptr(self.device)))
-        return rt.give_back(rank, a, "snds_r")
+        out = rt.give_back(rank, a, "snds_r")  # synchronises the stream unless the input was a CUDA tensor
+        self._raise_if_peer_failed(synced=a.kind != "cuda")
+        return out
 
     def nsga2_select(self, merged_fitness, pop_size: int, return_details: bool = False):
         L = _lib.lib()
@@ -151,5 +172,8 @@ class ShardedSelector:
                                                  rt.stream_ptr(self.device))
             )
         if return_details:
-            return (rt.give_back(order, f, "ssel_o"), rt.give_back(rank, f, "ssel_r"), rt.give_back(crowd, f, "ssel_c"))
-        return rt.give_back(order, f, "ssel_o")
+            out = (rt.give_back(order, f, "ssel_o"), rt.give_back(rank, f, "ssel_r"), rt.give_back(crowd, f, "ssel_c"))
+        else:
+            out = rt.give_back(order, f, "ssel_o")
+        self._raise_if_peer_failed(synced=f.kind != "cuda")
+        return out

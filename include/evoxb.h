@@ -142,18 +142,32 @@ EVOXB_API int evoxb_sbx_pm_clip_f32(const float *pop, int64_t n, int d, const fl
                                     float pro_c, float dis_c, float pro_m, float dis_m, uint32_t seed,
                                     uint32_t generation, float *out, evoxb_stream_t stream);
 EVOXB_API int evoxb_dtlz2_f32(const float *x, int64_t n, int d, int m, float *f, evoxb_stream_t stream);
+/* evoxb_lsmop1_f32 = LSMOP1.evaluate (src/evox/problems/numerical/lsmop.py:127-141 with _calc_g :88-111 and the
+ * sphere inner function, problems/numerical/sphere.py:5-6): x (n, d) -> f (n, m), 2 <= m <= 16.
+ * sublen[i] / start[i] (host arrays of m ints) are the reference's `self.sublen[i]` and `self.len[i]`
+ * (lsmop.py:44-54: logistic-map weights, floor(c / sum(c) * d / 5), cumulative sum of 5 * sublen).        */
+EVOXB_API int evoxb_lsmop1_f32(const float *x, int64_t n, int d, int m, const int32_t *sublen, const int32_t *start,
+                               float *f, evoxb_stream_t stream);
 
 /* ---- e: multi-GPU ranking, one process per GPU (no counterpart in the reference, whose tell() is
  * replicated on every device: src/evox/workflows/std_workflow.py:194, :341) ---------------------------
  * The bit-packed dominance matrix is sharded by COLUMN chunk (4096 dominated individuals per chunk,
  * chunks dealt cyclically to the ranks); every rank keeps all rows of its chunks and the dominator
  * counts of its columns, so counts never cross GPUs.  Per front the ranks exchange one bit per
- * individual (ncclAllGather, N/8 bytes in total).  Every rank receives the full rank vector.
- * NCCL is loaded at run time (libnccl.so.2 of the process, or $EVOXB_NCCL_LIB).
+ * individual (N/8 bytes in total).  Every rank receives the full rank vector.  Three exchanges exist:
+ *   2  data-flow kernel (peel_flow.cuh): one persistent kernel per GPU, tagged 8-byte words stored
+ *      straight into the peers' memory (CUDA IPC over NVLink), no grid-wide barrier;
+ *   1  grid-wide peer-memory kernel (peel.cuh): same transport, two grid syncs per front;
+ *   0  one ncclAllGather per front, host check every 4 fronts (when peers cannot be mapped).
+ * The library picks 2 or 1 from the population size per GPU (both stream-ordered, no host sync) and
+ * falls back to 0.  NCCL is loaded at run time (libnccl.so.2 of the process, or $EVOXB_NCCL_LIB).
  *   evoxb_comm_unique_id : rank 0 makes the 128-byte NCCL id; the caller broadcasts it (any transport)
  *   evoxb_comm_create    : collective; call with the GPU of this rank current
- * The sharded entry points synchronise `stream` once per 4 fronts (termination check) and must be
- * called by all ranks with the same arguments.  Supports m <= 16.                                   */
+ * The sharded entry points must be called by all ranks with the same arguments.  Supports m <= 16.
+ * Peer time-out: a kernel that waits longer than the time-out (default 4 s, evoxb_comm_set_timeout_ms)
+ * for a peer gives up: the call's ranks are all -1, the error is sticky (evoxb_comm_poll_error != 0)
+ * and every later sharded call on the communicator returns EVOXB_E_NCCL without launching; destroy the
+ * communicator on every rank and create a new one.                                                   */
 typedef struct evoxb_comm evoxb_comm_t;
 EVOXB_API int evoxb_comm_unique_id(void *id128);
 EVOXB_API int evoxb_comm_create(const void *id128, int rank, int nranks, evoxb_comm_t **out);
@@ -163,6 +177,14 @@ EVOXB_API int evoxb_comm_destroy(evoxb_comm_t *comm);
  * to one ncclAllGather per front.  error: 1 if a peer did not answer within ~4 s during the last
  * call.  fronts: number of fronts of the last peer-memory call.  Synchronous (small D2H copies).    */
 EVOXB_API int evoxb_comm_status(evoxb_comm_t *comm, int *p2p_enabled, int *error, int *fronts);
+/* 1 after a peer time-out on this communicator, else 0.  Reads a host word the kernels raise: no device
+ * synchronisation, so it is meaningful for calls whose work has completed (after a stream sync).      */
+EVOXB_API int evoxb_comm_poll_error(evoxb_comm_t *comm);
+/* How long a kernel waits for a peer GPU before giving up (first calls can be skewed by seconds of
+ * lazy initialisation on another rank).  Same value on every rank; takes effect from the next call.  */
+EVOXB_API int evoxb_comm_set_timeout_ms(evoxb_comm_t *comm, int64_t ms);
+/* Exchange used by the last sharded call on this communicator: 0, 1 or 2 as listed above.           */
+EVOXB_API int evoxb_comm_last_path(evoxb_comm_t *comm);
 EVOXB_API int evoxb_shard_plan(int64_t n, int rank, int nranks, int *first_chunk, int *chunk_stride,
                                int *local_chunks, int *total_chunks);
 EVOXB_API int evoxb_nds_sharded_workspace_bytes(int64_t n, int m, int rank, int nranks, size_t *bytes);

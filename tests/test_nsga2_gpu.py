@@ -101,3 +101,35 @@ def test_nsga2_converges_on_dtlz2_config1():
     start = vo.dtlz2(np.random.default_rng(1).random((100, 12), dtype=np.float32), 3)
     assert vo.igd(fit, pf) < 0.12 < vo.igd(start, pf)
     assert np.abs(np.linalg.norm(fit, axis=1) - 1).mean() < 0.05  # on the sphere: g -> 0
+
+
+def test_lsmop1_reference_spot_values(kats):
+    """tests/test_lsmop.py:10-29 through the CUDA kernel (input regenerated with oracle/jax_prng.py)."""
+    from evox_myc_b200 import nsga2
+    from oracle import jax_prng
+
+    k = kats["lsmop1_100x300_prng0"]
+    upper = np.hstack([np.ones(2), 10 * np.ones(298)]).astype(np.float32)
+    data = jax_prng.uniform_array_f32(0, (100, 300), 0.0, upper)
+    prob = nsga2.LSMOP1(d=300, m=3)
+    r, _ = prob.evaluate(None, torch.from_numpy(data).cuda())
+    r = r.cpu().numpy()
+    assert list(r.shape) == k["shape"]
+    for i, j, v in k["spot"]:
+        assert abs(float(r[i, j]) - v) < k["atol"]
+
+
+@pytest.mark.parametrize("n,m,d", [(1000, 3, 300), (257, 10, 1000), (64, 2, 40), (33, 16, 1600)])
+def test_lsmop1_matches_restatement(n, m, d):
+    from evox_myc_b200 import nsga2
+    from oracle import lsmop_oracle
+
+    rng = np.random.default_rng(n + m)
+    x = rng.random((n, d), dtype=np.float32)
+    x[:, m - 1 :] *= np.float32(10)
+    prob = nsga2.LSMOP1(d=d, m=m)
+    assert (prob.sublen, prob.len) == lsmop_oracle.lsmop_groups(d, m)
+    got, _ = prob.evaluate(None, torch.from_numpy(x).cuda())
+    want = lsmop_oracle.lsmop1(x, m)
+    # float32 sums of up to ~700 squares in a different association: 1e-5 relative
+    np.testing.assert_allclose(got.cpu().numpy(), want, rtol=1e-5, atol=1e-30)

@@ -24,9 +24,17 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, cases, out, no_p2p=False):
-    if no_p2p:
-        os.environ["EVOXB_NO_P2P"] = "1"
+PATH_ENV = {
+    "data_flow": {"EVOXB_PEEL_MODE": "flow"},      # peel_flow_kernel across the GPUs (where every rank owns a chunk)
+    "grid_peer": {"EVOXB_PEEL_MODE": "grid"},      # peel_p2p_kernel
+    "nccl_allgather": {"EVOXB_NO_P2P": "1"},       # one ncclAllGather per front
+    "auto": {},                                    # whatever the library picks
+}
+
+
+def _worker(rank, world, port, cases, out, path="auto"):
+    os.environ.update(PATH_ENV[path])
+    no_p2p = path == "nccl_allgather"
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch
@@ -62,36 +70,52 @@ def _worker(rank, world, port, cases, out, no_p2p=False):
         if err: why.append("a peer timed out")
         if p2p == no_p2p: why.append(f"peer-memory path enabled={p2p}, expected {not no_p2p}")
         if p2p and fronts != int(w_rank.max()) + 1: why.append(f"fronts {fronts} != {int(w_rank.max()) + 1}")
+        used = sel.last_path()
+        nchunks = -(-n // 4096)
+        if path == "data_flow" and world <= nchunks <= 128 and not used.startswith("data-flow"): why.append(f"ran on '{used}'")
+        if path == "grid_peer" and not used.startswith("grid-wide"): why.append(f"ran on '{used}'")
+        if path == "nccl_allgather" and not used.startswith("ncclAllGather"): why.append(f"ran on '{used}'")
         res.append((kind, n, m, "; ".join(why)))
         sel.close()
     out[rank] = res
     dist.destroy_process_group()
 
 
+# small populations (fewer chunks than ranks at the larger world sizes), then enough chunks for every rank
 CASES = [("uniform", 5000, 3, 1), ("nasty", 9001, 4, 2), ("uniform", 20000, 2, 3), ("integer_grid", 12000, 3, 4),
-         ("uniform", 40000, 5, 5)]
+         ("uniform", 40000, 5, 5), ("uniform", 70000, 3, 6), ("nasty", 150001, 4, 7)]
+# BASELINE config 4 at full size: 64 chunks, 8 per rank at world 8
+FULL = [("uniform", 262144, 5, 8)]
 
 
-def _run(world, no_p2p=False):
+def _run(world, path="auto", cases=CASES):
     import torch.multiprocessing as mp
 
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_worker, args=(world, _free_port(), CASES, out, no_p2p), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), cases, out, path), nprocs=world, join=True)
     assert len(out) == world
     for r in range(world):
         for kind, n, m, why in out[r]:
-            assert not why, f"rank {r} of {world}: {kind} {n}x{m}: {why}"
+            assert not why, f"rank {r} of {world} ({path}): {kind} {n}x{m}: {why}"
 
 
-@pytest.mark.parametrize("no_p2p", [False, True], ids=["peer_memory", "nccl_allgather"])
-def test_sharded_world_size_1(no_p2p):
-    _run(1, no_p2p)
+@pytest.mark.parametrize("path", ["data_flow", "grid_peer", "nccl_allgather", "auto"])
+def test_sharded_world_size_1(path):
+    _run(1, path)
 
 
-@pytest.mark.parametrize("no_p2p", [False, True], ids=["peer_memory", "nccl_allgather"])
+@pytest.mark.parametrize("path", ["data_flow", "grid_peer", "nccl_allgather", "auto"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_sharded_multi_gpu(world, no_p2p):
+def test_sharded_multi_gpu(world, path):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    _run(world, no_p2p)
+    _run(world, path)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_config4_full_size(world):
+    """N = 262144, M = 5 sharded (ranks, crowding and survivor order against the C oracle on every rank)."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    _run(world, "auto", FULL)
