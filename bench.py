@@ -55,17 +55,38 @@ def make_fitness(n: int, m: int, seed: int = 0) -> np.ndarray:
     return np.random.default_rng(seed).random((n, m), dtype=np.float32)
 
 
-def ncu_traffic_per_launch(kernel_substr: str, n: int, m: int):
+def library_source_hash() -> str:
+    """sha256 (16 hex digits) over the CUDA sources of libevoxb.so -- ties a committed ncu capture to the code."""
+    import glob
+    import hashlib
+
+    h = hashlib.sha256()
+    for path in sorted(glob.glob(os.path.join(ROOT, "evox-myc_b200", "csrc", "*.cu*"))):
+        h.update(open(path, "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic_per_launch(kernel_substr: str, n: int, m: int, world: int = 1):
     """DRAM bytes (read + write) per launch of a kernel from the committed ncu launch list of the same
-    workload (profiles/), or None when no capture of this workload is committed."""
+    workload (profiles/).  The capture's side file (<csv>.meta.json, written by the capture script) holds
+    the source hash it was taken from; a capture of older kernels is refused (traffic null, reason given)."""
     import csv
     import glob
 
+    tag = f"N{n}_M{m}" + (f"_w{world}" if world > 1 else "")
     best = None
-    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", f"launches_*_N{n}_M{m}_v*.csv"))):
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", f"launches_*_{tag}_v*.csv"))):
         best = path  # the latest version of the latest round
     if best is None:
-        return None, None
+        return None, "no committed ncu capture of this workload"
+    meta = best + ".meta.json"
+    rel = os.path.relpath(best, ROOT)
+    try:
+        want = json.load(open(meta))["src_hash"]
+    except Exception:
+        return None, f"{rel} has no source hash beside it (taken before the kernels changed?)"
+    if want != library_source_hash():
+        return None, f"{rel} is stale: taken from sources {want}, library is {library_source_hash()}"
     tot, launches = 0.0, 0
     try:
         rows = list(csv.reader(l for l in open(best) if l.startswith('"')))
@@ -77,9 +98,11 @@ def ncu_traffic_per_launch(kernel_substr: str, n: int, m: int):
                     tot += float(r[vi].replace(",", ""))
                 elif r[mi] == "gpu__time_duration.sum":
                     launches += 1
-    except Exception:
-        return None, None
-    return (tot / launches, os.path.relpath(best, ROOT)) if launches and tot else (None, None)
+    except Exception as ex:
+        return None, f"{rel}: unreadable ({ex!r})"
+    if not (launches and tot):
+        return None, f"{rel} holds no launch of {kernel_substr}"
+    return tot / launches, f"ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, {rel} (sources {want})"
 
 
 def measured_peaks():
@@ -256,33 +279,41 @@ def run_gpu_arm(args, n, m, desc):
         torch.cuda.synchronize(dev)
 
     # ---- device-resident timing -------------------------------------------------------------
+    # K steps enqueued back to back (no host round trip inside the timed region); one event pair around the
+    # whole run gives `value`, one pair per step gives best / median.  Stage times come from a separate,
+    # untimed pass with the library's stage events enabled.
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()  # nvidia-smi needs a moment to start; samples are filtered to the busy ones
     for _ in range(max(args.warmup, 3)):
         step_dev()
-    _lib.profile_enable(True)
     barrier()
     launches0 = _lib.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage_acc: dict[str, float] = {}
-    ev0.record()
-    for _ in range(args.steps):
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    evs[0].record()
+    for i in range(args.steps):
         step_dev()
-        # stage events of this step are read after the loop would need one event set per step;
-        # reading here synchronises on the step's last event only (no extra work is timed out)
-        for k, v in _lib.profile_read().items():
-            stage_acc[k] = stage_acc.get(k, 0.0) + v
-    ev1.record()
+        evs[i + 1].record()
     barrier()
     launches = _lib.launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
-    _lib.profile_enable(False)
-    t_ms = ev0.elapsed_time(ev1) / args.steps
+    t_ms = evs[0].elapsed_time(evs[-1]) / args.steps
+    per_step = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps))
     if dist is not None:
-        tt = torch.tensor([t_ms], device=dev)
+        tt = torch.tensor([t_ms, per_step[0], per_step[len(per_step) // 2]], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_ms = float(tt.item())
+        t_ms, best_ms, median_ms = (float(v) for v in tt.tolist())
+    else:
+        best_ms, median_ms = per_step[0], per_step[len(per_step) // 2]
+    _lib.profile_enable(True)
+    stage_acc: dict[str, float] = {}
+    prof_steps = min(args.steps, 10)
+    for _ in range(prof_steps):
+        step_dev()
+        for k, v in _lib.profile_read().items():  # synchronises on the step's last stage event
+            stage_acc[k] = stage_acc.get(k, 0.0) + v
+    _lib.profile_enable(False)
+    barrier()
 
     # ---- end-to-end through the public API with host buffers -----------------------------------
     for _ in range(2):
@@ -300,13 +331,32 @@ def run_gpu_arm(args, n, m, desc):
     h2d = x_host.nbytes
     d2h = int(np.asarray(out).nbytes)
 
+    # ---- what ran, and is it right (outside every timed region) ------------------------------
+    parity = None
+    exchange = None
+    if world > 1:
+        order_s, rank_s, crowd_s = ctx.nsga2_select(x_dev, pop, return_details=True)
+        p2p, peer_err, fronts = ctx.status()
+        exchange = {"path": ctx.last_path(), "peer_memory": p2p, "error": peer_err, "fronts": fronts}
+        if rank == 0 and not args.no_parity:
+            from oracle import c_oracle
+
+            w_order, w_rank, w_crowd = c_oracle.nsga2_select(x_host, pop, nthreads=host_cores())
+            fin = np.isfinite(w_crowd)
+            crowd_np = crowd_s.cpu().numpy()
+            parity = {"ranks_equal": bool(np.array_equal(rank_s.cpu().numpy(), w_rank)),
+                      "order_equal": bool(np.array_equal(order_s.cpu().numpy(), w_order)),
+                      "crowding_rtol_1e-6": bool(np.array_equal(np.isfinite(crowd_np), fin)
+                                                 and np.allclose(crowd_np[fin], w_crowd[fin], rtol=1e-6, atol=0)),
+                      "checker": "oracle/nds_oracle.c on rank 0, full size, after the timed regions"}
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return
 
     hbm_gbs, peak_src, sm_max = measured_peaks()
-    stages = {k: v / args.steps for k, v in stage_acc.items()}
+    stages = {k: v / prof_steps for k, v in stage_acc.items()}
     pairs = float(n) * float(n)
     peel_ms = stages.get("peel")
     cnt_ms = stages.get("dominator_count")
@@ -319,14 +369,20 @@ def run_gpu_arm(args, n, m, desc):
     alg_bytes = float(n) * n / 8.0 / world
     real_bytes = alg_bytes * (0.5 + 0.5 * 4096.0 / n) if tri else alg_bytes  # chunks c >= row/4096 only
     roofline = None
-    ncu_bytes, ncu_src = ncu_traffic_per_launch("peel_persistent_kernel", n, m) if world == 1 else (None, None)
+    if world == 1:
+        flow_possible = n <= 131072 and m <= 16
+        peel_kernel = ("peel_flow_kernel or peel_persistent_kernel (both enqueued, front-0 size decides on the device)"
+                       if flow_possible else "peel_persistent_kernel")
+    else:
+        peel_kernel = {"data-flow peer-memory kernel": "peel_flow_kernel (tagged words stored to the peers over NVLink)",
+                       "grid-wide peer-memory kernel": "peel_p2p_kernel (tagged words stored to the peers over NVLink)",
+                       }.get(exchange["path"], "front_subtract_kernel (+ detect / ncclAllGather / expand per front)")
+    ncu_bytes, ncu_src = ncu_traffic_per_launch("peel_persistent_kernel" if world == 1 else "peel_p2p_kernel", n, m, world)
     if peel_ms:
         ach = alg_bytes / (peel_ms * 1e-3) / 1e9
-        roofline = {"kernel": "peel_persistent_kernel" if world == 1 else "front_subtract_kernel (+ detect/all-gather/expand per front)",
+        roofline = {"kernel": peel_kernel,
                     "bound": "hbm", "achieved": ach, "peak": hbm_gbs, "unit": "GB/s",
-                    "frac": ach / hbm_gbs, "traffic": ncu_bytes,
-                    "traffic_source": (f"ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, {ncu_src}" if ncu_bytes
-                                       else "no committed ncu capture of this workload"),
+                    "frac": ach / hbm_gbs, "traffic": ncu_bytes, "traffic_source": ncu_src,
                     "triangle_bytes": real_bytes,
                     "executed_gbs": real_bytes / (peel_ms * 1e-3) / 1e9, "executed_frac": real_bytes / (peel_ms * 1e-3) / 1e9 / hbm_gbs,
                     "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": peel_ms}
@@ -373,10 +429,16 @@ def run_gpu_arm(args, n, m, desc):
                    "step": "non_dominated_sort + worst-rank mask + crowding_distance + survivor order (nsga2.py:90-96)",
                    "l2": "working set (bit-packed dominance matrix, N^2/8 bytes per step) exceeds the 126 MB L2"
                          if n * n / 8 / world > 126e6 else "L2 flushed by the matrix rewrite of each step",
-                   "parallelism": "single GPU" if world == 1 else f"dominance matrix sharded by column chunk over {world} GPUs, one ncclAllGather of N/8 bytes per front"},
+                   "cores": host_cores(),
+                   "parallelism": "single GPU" if world == 1 else
+                   f"dominance matrix sharded by column chunk over {world} GPUs; front bitmask (N/8 bytes per front) exchanged by: {exchange['path']}"},
         "e2e": {"value": pairs / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
+        "ms_per_step_best": best_ms, "ms_per_step_median": median_ms,
+        "timing": "CUDA events on the launching stream; K steps enqueued back to back, max over ranks",
+        "exchange": exchange,
+        "parity": parity,
         "clocks": clocks,
         "roofline": roofline,
         "kernels": extra,
@@ -455,6 +517,7 @@ def main():
     ap.add_argument("--workload", default="c4")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-nsga2", action="store_true", help="skip the NSGA-II generations/s measurement")
+    ap.add_argument("--no-parity", action="store_true", help="multi-GPU: skip the full-size oracle comparison on rank 0")
     args = ap.parse_args()
     n, m, desc = parse_workload(args.workload)
     if args.impl == "reference":

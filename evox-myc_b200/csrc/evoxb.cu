@@ -320,6 +320,7 @@ static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &
         for (int sh = 0; sh < 32; sh += 8) { pp.kind[pp.count] = 0; pp.shift[pp.count++] = sh; }
         if (m > 2) { pp.kind[pp.count] = 1; pp.shift[pp.count++] = 0; }  // S' exceeds 32 bits only with >= 2 terms
     }
+    pp.fast_first = pp.count;  // the key_0 passes alone are the fast path (presort.cuh)
     for (int sh = 0; sh < 32; sh += 8) { pp.kind[pp.count] = 2; pp.shift[pp.count++] = sh; }
     int blocks = 0;
     if (int rc = coop_blocks((const void *)presort_coop_kernel, 256, 2, &blocks)) return rc;
@@ -332,7 +333,8 @@ static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &
     int *urq = L.uid_row_q, *ucq = L.uid_col_q;
     float *tmin = L.tile_min1, *tmax = L.tile_max1;
     float *xt = L.xt;
-    void *args[] = {&x, &nn, &mm, &npad, &pp, &pa, &pb, &hist, &tile_max, &hp, &xt, &perm, &ur, &uc, &urq, &ucq, &tmin, &tmax};
+    int *slow_flag = &L.ctrl->presort_slow;  // zeroed with the rest of PeelCtrl before this launch
+    void *args[] = {&x, &nn, &mm, &npad, &pp, &pa, &pb, &hist, &tile_max, &hp, &xt, &perm, &ur, &uc, &urq, &ucq, &tmin, &tmax, &slow_flag};
     EVOXB_CUDA(cudaLaunchCooperativeKernel((const void *)presort_coop_kernel, dim3(blocks), dim3(256), args, 0, s));
     ++g_launches;
     return 0;
@@ -390,7 +392,9 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     if (fl.ok) {
         if (peel_mode_env() == 1) return run_peel_flow(L, n, rank, perm, fl, -1, s);
         if (peel_use_flow(n, m)) {
-            front0_limit = (int)(n / 16);
+            // front 0 is the smallest of the early fronts: n / 96 separates the measured cases (uniform M = 3..5 at
+            // 32768..131072 rows, NSGA-II on DTLZ2 from random to converged populations) by which kernel is faster
+            front0_limit = (int)(n / 96);
             if (int rc = run_peel_flow(L, n, rank, perm, fl, front0_limit, s)) return rc;
         }
     }
@@ -455,17 +459,17 @@ static NcclApi &nccl_api() {
 
 // Which fused kernel peels across GPUs.  The data-flow kernel needs every rank to own at least one chunk (a
 // rank without columns would publish nothing, and nobody would wait for it to have read a buffer before it is
-// reused).  It wins where a front is little work per GPU (latency: many GPUs or a small population); the
-// grid-wide kernel keeps the cases with megabytes per front and GPU.  Must be the same on every rank.
+// reused).  Measured on 2 and 8 B200s at N = 262144, M = 5 (10 000 members per front) the grid-wide kernel
+// is faster (8 GPUs: peel 0.98 ms against 1.59 ms), so the data-flow kernel is kept for the populations where
+// it wins on one GPU too: many small fronts.  Must be the same on every rank.
 static bool sharded_use_flow(int64_t n, int m, int nchunks, int nranks) {
-    (void)m;
     if (nchunks < nranks || nchunks > kFlowMaxChunks) return false;
     static const int mode = [] {
         const char *ev = getenv("EVOXB_PEEL_MODE");
         return !ev ? 0 : !strcmp(ev, "flow") ? 1 : !strcmp(ev, "grid") ? 2 : 0;
     }();
     if (mode) return mode == 1;
-    return n / nranks <= 32768;
+    return peel_use_flow(n, m);
 }
 
 // Row-sharded^T ranking: every GPU presorts (same permutation everywhere), builds and keeps the
@@ -482,6 +486,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         return fail(EVOXB_E_UNSUPPORTED, "n = %lld exceeds %d rows", (long long)n, kMaxChunks * kChunkCols);
     NcclApi &nc = nccl_api();
     prof.mark("prep", s);
+    EVOXB_CUDA(cudaMemsetAsync(L.ctrl, 0, sizeof(PeelCtrl), s));
     EVOXB_CUDA(cudaMemsetAsync(L.count, 0, sizeof(int) * (size_t)L.npad, s));
     if (int rc = run_presort(fitness, n, m, L, s)) return rc;
 

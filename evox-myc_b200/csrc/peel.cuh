@@ -386,6 +386,7 @@ struct PeelCtrl {
     int cnt[2][kMaxChunks];  // members per region of the current / next front (double-buffered)
     int fronts_done;         // number of fronts peeled (written at exit)
     int front0;              // size of front 0 (front0_size_kernel); only set when both peel kernels are enqueued
+    int presort_slow;        // raised by the presort when a run of equal key_0 is too long for its fast path
 };
 
 // K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).

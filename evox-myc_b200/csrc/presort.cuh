@@ -47,14 +47,18 @@ struct PresortPasses {
     int count;
     int kind[kMaxPasses];   // 0: low 32 bits of S', 1: high bits of S', 2: key of objective 0
     int shift[kMaxPasses];
+    int fast_first;         // index of the first key_0 pass: passes [fast_first, count) alone sort by key_0
 };
+
+constexpr int kPresortRunMax = 32;  // longest run of equal key_0 the fast path orders in place
 
 __global__ void __launch_bounds__(256)
 presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, PresortPasses passes,
                     uint32_t *__restrict__ perm_a, uint32_t *__restrict__ perm_b, uint32_t *__restrict__ hist_g,
                     int *__restrict__ tile_max, int *__restrict__ hp, float *__restrict__ xt, int *__restrict__ perm_out,
                     int *__restrict__ uid_row, int *__restrict__ uid_col, int *__restrict__ uid_row_q,
-                    int *__restrict__ uid_col_q, float *__restrict__ tile_min1, float *__restrict__ tile_max1) {
+                    int *__restrict__ uid_col_q, float *__restrict__ tile_min1, float *__restrict__ tile_max1,
+                    int *__restrict__ slow_flag) {
     __shared__ CoopSortSmem csm;
     __shared__ uint32_t sh_warp[8];
     __shared__ int sh_carry;
@@ -65,19 +69,64 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
     cgx::grid_group grid = cgx::this_grid();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+    // Fast path: rows are first sorted by key_0 alone (4 of the 9 passes).  The order by (key_0, S') differs
+    // from that only inside runs of equal key_0, which are short for real-valued objectives (a few thousand
+    // pairs among 262144 uniform floats): every run of at most kPresortRunMax rows is put in S' order in place
+    // by the thread that finds its head (stable, so the result is the permutation the full sort would give).
+    // A longer run (tie-heavy data: integer grids, duplicated rows) raises *slow_flag (zeroed by the host)
+    // and the whole grid falls back to all passes.
     const uint32_t *src = nullptr;  // nullptr = identity permutation
     uint32_t *dst = perm_a;
-    for (int ps = 0; ps < passes.count; ++ps) {
-        const int kind = passes.kind[ps];
-        auto key = [=](int, uint32_t row) -> uint32_t {
-            const float *r = x + (int64_t)row * m;
-            if (kind == 2) return float_to_key(r[0]);
-            const unsigned long long sp = sum_tail_keys(r, m);
-            return kind == 0 ? (uint32_t)sp : (uint32_t)(sp >> 32);
-        };
-        coop_radix_pass(grid, csm, key, 1, n, npad, src, false, dst, hist_g, passes.shift[ps]);
-        src = dst;
-        dst = (dst == perm_a) ? perm_b : perm_a;
+    auto run_passes = [&](int first, int last) {
+        for (int ps = first; ps < last; ++ps) {
+            const int kind = passes.kind[ps];
+            auto key = [=](int, uint32_t row) -> uint32_t {
+                const float *r = x + (int64_t)row * m;
+                if (kind == 2) return float_to_key(r[0]);
+                const unsigned long long sp = sum_tail_keys(r, m);
+                return kind == 0 ? (uint32_t)sp : (uint32_t)(sp >> 32);
+            };
+            coop_radix_pass(grid, csm, key, 1, n, npad, src, false, dst, hist_g, passes.shift[ps]);
+            src = dst;
+            dst = (dst == perm_a) ? perm_b : perm_a;
+        }
+    };
+    run_passes(passes.fast_first, passes.count);
+    if (passes.fast_first > 0) {
+        uint32_t *cur = const_cast<uint32_t *>(src);
+        for (int p = blockIdx.x * 256 + threadIdx.x; p < n; p += gridDim.x * 256) {
+            const uint32_t k0 = float_to_key(x[(int64_t)__ldcg(cur + p) * m]);
+            if (p > 0 && float_to_key(x[(int64_t)__ldcg(cur + p - 1) * m]) == k0) continue;  // not a head
+            int len = 1;
+            while (p + len < n && len <= kPresortRunMax && float_to_key(x[(int64_t)__ldcg(cur + p + len) * m]) == k0) ++len;
+            if (len == 1) continue;
+            if (len > kPresortRunMax) {
+                atomicOr(slow_flag, 1);
+                continue;
+            }
+            // stable insertion sort of the run by S' (rows of equal (key_0, S') keep their input order)
+            uint32_t rows[kPresortRunMax];
+            unsigned long long sp[kPresortRunMax];
+            for (int i = 0; i < len; ++i) {
+                const uint32_t row = __ldcg(cur + p + i);
+                const unsigned long long v = sum_tail_keys(x + (int64_t)row * m, m);
+                int j = i;
+                while (j > 0 && sp[j - 1] > v) {
+                    sp[j] = sp[j - 1];
+                    rows[j] = rows[j - 1];
+                    --j;
+                }
+                sp[j] = v;
+                rows[j] = row;
+            }
+            for (int i = 0; i < len; ++i) cur[p + i] = rows[i];
+        }
+        grid.sync();
+        if (*reinterpret_cast<volatile int *>(slow_flag) != 0) {
+            src = nullptr;
+            dst = perm_a;
+            run_passes(0, passes.count);
+        }
     }
 
     // ---- heads of equal-(key_0, S') runs, NaN flags (kept in uid_col for now), tile maxima ----
