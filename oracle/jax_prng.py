@@ -114,3 +114,27 @@ def normal_f32(seed: int, shape: tuple[int, ...]) -> np.ndarray:
     u = uniform_f32(prng_key(seed), n, lo, hi)
     out = (np.float32(np.sqrt(2.0)) * _erfinv_f32(u)).astype(np.float32)
     return out.reshape(shape)
+
+
+def split(key: tuple[int, int], num: int) -> list[tuple[int, int]]:
+    """``jax.random.split(key, num)`` (threefry, non-partitionable layout): counters 0 .. 2 num - 1 are hashed
+    in two halves and the 2 num output words, read in order, are the num new keys."""
+    flat = random_bits32(key, 2 * num)
+    return [(int(flat[2 * i]), int(flat[2 * i + 1])) for i in range(num)]
+
+
+def randint_scalar(key: tuple[int, int], minval: int, maxval: int) -> int:
+    """``jax.random.randint(key, (), minval, maxval)`` for int32 (jax/_src/random.py ``_randint``): two 32-bit
+    draws from the two halves of ``split(key)``, combined as ((hi % span) * (2^32 % span) + lo % span) % span
+    in uint32 arithmetic.  Restated from the published JAX 0.4.x source; no reference test pins it."""
+    k1, k2 = split(key, 2)
+    hi = int(random_bits32(k1, 1)[0])
+    lo = int(random_bits32(k2, 1)[0])
+    span = (maxval - minval) & 0xFFFFFFFF
+    if maxval <= minval:
+        span = 1
+    mult = (1 << 16) % span
+    mult = ((mult * mult) & 0xFFFFFFFF) % span  # == 2**32 % span while span <= 2**16 (uint32 product wraps beyond)
+    off = (((hi % span) * mult) & 0xFFFFFFFF) + (lo % span)
+    off = (off & 0xFFFFFFFF) % span
+    return minval + off
