@@ -14,6 +14,7 @@ from .operators import (  # noqa: F401
     nsga2_select,
     nsga3_last_rank,
 )
+from .nsga3 import UniformSampling, nsga3_select  # noqa: F401
 from .utils import dominate_relation  # noqa: F401
 
 __all__ = [
@@ -24,5 +25,7 @@ __all__ = [
     "NonDominate",
     "nsga2_select",
     "nsga3_last_rank",
+    "nsga3_select",
+    "UniformSampling",
     "dominate_relation",
 ]

@@ -26,6 +26,8 @@ EXPORTS = [
     "evoxb_crowding_noalloc_f32",
     "evoxb_nsga2_select_workspace_bytes",
     "evoxb_nsga2_select_f32",
+    "evoxb_nsga3_select_workspace_bytes",
+    "evoxb_nsga3_select_f32",
     "evoxb_kth_rank_workspace_bytes",
     "evoxb_kth_rank_i32",
     "evoxb_non_dominate_select_f32",
@@ -78,6 +80,9 @@ def lib() -> ctypes.CDLL:
         L.evoxb_crowding_noalloc_f32.argtypes = [vp, vp, i64, i32, vp, vp]
         L.evoxb_nsga2_select_workspace_bytes.argtypes = [i64, i32, ctypes.POINTER(sz)]
         L.evoxb_nsga2_select_f32.argtypes = [vp, i64, i32, i64, vp, vp, vp, vp, sz, vp]
+        L.evoxb_nsga3_select_workspace_bytes.argtypes = [i64, i32, i64, ctypes.POINTER(sz)]
+        L.evoxb_nsga3_select_f32.argtypes = [vp, i64, i32, i64, vp, i64, ctypes.POINTER(ctypes.c_uint32), vp,
+                                             ctypes.POINTER(ctypes.c_uint32), vp, vp, vp, vp, vp, sz, vp]
         L.evoxb_kth_rank_workspace_bytes.argtypes = [i64, ctypes.POINTER(sz)]
         L.evoxb_kth_rank_i32.argtypes = [vp, i64, i64, vp, vp, sz, vp]
         L.evoxb_non_dominate_select_f32.argtypes = [vp, i64, i32, i64, vp, vp, sz, vp]

@@ -17,6 +17,7 @@
 #include "select.cuh"
 #include "variation.cuh"
 #include "tail.cuh"
+#include "nsga3.cuh"
 
 namespace evoxb {
 
@@ -1183,6 +1184,129 @@ EVOXB_API int evoxb_gather_rows_f32(const float *src, int64_t n, int64_t d, cons
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     gather_rows_kernel<<<(unsigned)div_up(k * d, 256), 256, 0, s>>>(src, d, idx, k, dst);
     EVOXB_LAUNCH_CHECK("gather_rows_kernel");
+    return 0;
+}
+
+}  // extern "C"
+
+// ---- NSGA-III environmental selection (nsga3.py:93-211) ---------------------------------------------------
+namespace evoxb {
+struct Nsga3Full {
+    Nsga3Layout n3;
+    NdsLayout nds;
+    int *rank;
+    size_t bytes;
+};
+static Nsga3Full nsga3_full_layout(void *ws, int64_t n, int m, int64_t r) {
+    Nsga3Full F{};
+    Carver c(ws);
+    F.rank = c.take<int>((size_t)(n > 0 ? n : 1));
+    {
+        char *sub = c.take<char>(0);
+        F.n3 = nsga3_layout(sub, n, m, r);
+        c.take<char>(F.n3.bytes);
+    }
+    {
+        char *sub = c.take<char>(0);
+        F.nds = nds_layout(sub, n, m, n);
+        c.take<char>(F.nds.bytes);
+    }
+    F.bytes = c.total();
+    return F;
+}
+}  // namespace evoxb
+
+extern "C" {
+
+EVOXB_API int evoxb_nsga3_select_workspace_bytes(int64_t n, int m, int64_t r, size_t *bytes) {
+    if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
+    if (int rc = check_common((const void *)1, n, m)) return rc;
+    if (r < 1) return fail(EVOXB_E_INVALID, "at least one reference point is needed (got %lld)", (long long)r);
+    *bytes = nsga3_full_layout(nullptr, n, m, r).bytes;
+    return 0;
+}
+
+EVOXB_API int evoxb_nsga3_select_f32(const float *fitness, int64_t n, int m, int64_t pop_size, const float *ref, int64_t r,
+                                     const uint32_t key[2], int32_t *selected_idx, uint32_t next_key[2], int32_t *rank_out,
+                                     int32_t *group_id_out, float *group_dist_out, float *norm_out, void *ws, size_t ws_bytes,
+                                     evoxb_stream_t stream) {
+    if (int rc = check_common(fitness, n, m)) return rc;
+    if (!nds_use_tri(m)) return fail(EVOXB_E_UNSUPPORTED, "NSGA-III selection supports m <= 16 (got %d)", m);
+    if (r < 1 || !ref) return fail(EVOXB_E_INVALID, "reference points missing (r = %lld)", (long long)r);
+    if (pop_size < 1 || pop_size >= n)
+        return fail(EVOXB_E_INVALID, "pop_size must be in [1, n) (got %lld, n = %lld)", (long long)pop_size, (long long)n);
+    if (!key || !selected_idx) return fail(EVOXB_E_INVALID, "null pointer");
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return fail(EVOXB_E_WORKSPACE, "workspace is null or not 256-byte aligned");
+    Nsga3Full F = nsga3_full_layout(ws, n, m, r);
+    if (ws_bytes < F.bytes) return fail(EVOXB_E_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, F.bytes);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    Profiler &prof = profiler();
+    prof.begin();
+    int *rank = rank_out ? rank_out : F.rank;
+    if (int rc = run_nds(fitness, n, m, rank, F.nds, s, prof)) return rc;
+
+    prof.mark("nsga3_normalise", s);
+    const Nsga3Layout &L = F.n3;
+    const int nn = (int)n, rr = (int)r;
+    const unsigned gb = (unsigned)div_up(n, 256);
+    EVOXB_CUDA(cudaMemsetAsync(L.hist, 0, sizeof(int) * (size_t)n, s));
+    EVOXB_CUDA(cudaMemsetAsync(L.info, 0, sizeof(int) * 64, s));
+    EVOXB_CUDA(cudaMemsetAsync(L.ideal_key, 0xff, sizeof(uint32_t) * (size_t)m, s));
+    EVOXB_CUDA(cudaMemsetAsync(L.worst_key, 0, sizeof(uint32_t) * (size_t)m, s));
+    EVOXB_CUDA(cudaMemsetAsync(L.ext_key, 0xff, sizeof(unsigned long long) * (size_t)m, s));
+    EVOXB_CUDA(cudaMemsetAsync(L.rho, 0, sizeof(int) * (size_t)r, s));
+    EVOXB_CUDA(cudaMemsetAsync(L.rho_last, 0, sizeof(int) * (size_t)r, s));
+    EVOXB_CUDA(cudaMemsetAsync(L.cursor, 0, sizeof(int) * (size_t)r, s));
+    rank_hist_kernel<<<gb, 256, 0, s>>>(rank, n, L.hist);
+    EVOXB_LAUNCH_CHECK("rank_hist_kernel");
+    kth_rank_kernel<<<1, 1024, 0, s>>>(L.hist, n, pop_size, L.info);  // last_rank = rank[argsort(rank)[pop_size]], nsga3.py:97-98
+    EVOXB_LAUNCH_CHECK("kth_rank_kernel");
+    n3_ideal_kernel<<<gb, 256, 0, s>>>(fitness, rank, nn, m, L.info, L.ideal_key);
+    EVOXB_LAUNCH_CHECK("n3_ideal_kernel");
+    n3_extreme_kernel<<<gb, 256, 0, s>>>(fitness, rank, nn, m, L.info, L.ideal_key, L.ext_key, L.worst_key);
+    EVOXB_LAUNCH_CHECK("n3_extreme_kernel");
+    n3_nadir_kernel<<<1, 32, 0, s>>>(fitness, m, L.ideal_key, L.ext_key, L.worst_key, L.norm, L.info);
+    EVOXB_LAUNCH_CHECK("n3_nadir_kernel");
+    n3_unit_rows_kernel<<<gb, 256, 0, s>>>(fitness, rank, nn, m, L.info, L.norm, L.xu, L.xnorm);
+    EVOXB_LAUNCH_CHECK("n3_unit_rows_kernel");
+    n3_unit_refs_kernel<<<(unsigned)div_up(r, 256), 256, 0, s>>>(ref, rr, m, L.yu);
+    EVOXB_LAUNCH_CHECK("n3_unit_refs_kernel");
+
+    prof.mark("nsga3_associate", s);
+    int *gid = group_id_out ? group_id_out : L.gid;
+    float *gdist = group_dist_out ? group_dist_out : L.gdist;
+#define EVOXB_N3_CASE(MM)                                                                          \
+    case MM:                                                                                       \
+        n3_associate_kernel<MM><<<gb, 256, 0, s>>>(L.xu, L.xnorm, nn, L.yu, rr, gid, gdist);      \
+        break;
+    switch (m) {
+        EVOXB_N3_CASE(1) EVOXB_N3_CASE(2) EVOXB_N3_CASE(3) EVOXB_N3_CASE(4) EVOXB_N3_CASE(5) EVOXB_N3_CASE(6)
+        EVOXB_N3_CASE(7) EVOXB_N3_CASE(8) EVOXB_N3_CASE(9) EVOXB_N3_CASE(10) EVOXB_N3_CASE(11) EVOXB_N3_CASE(12)
+        EVOXB_N3_CASE(13) EVOXB_N3_CASE(14) EVOXB_N3_CASE(15) EVOXB_N3_CASE(16)
+    }
+#undef EVOXB_N3_CASE
+    EVOXB_LAUNCH_CHECK("n3_associate_kernel");
+
+    prof.mark("nsga3_niche", s);
+    n3_count_kernel<<<gb, 256, 0, s>>>(rank, gid, nn, rr, L.info, L.rho, L.rho_last, L.keep);
+    EVOXB_LAUNCH_CHECK("n3_count_kernel");
+    n3_offsets_kernel<<<1, 1024, 0, s>>>(L.rho_last, rr, L.off);
+    EVOXB_LAUNCH_CHECK("n3_offsets_kernel");
+    n3_fill_kernel<<<gb, 256, 0, s>>>(rank, gid, nn, rr, L.info, L.off, L.cursor, L.members);
+    EVOXB_LAUNCH_CHECK("n3_fill_kernel");
+    NicheArgs na{};
+    na.n = nn; na.r = rr; na.pop = (int)pop_size;
+    na.key0 = key[0]; na.key1 = key[1];
+    na.rho = L.rho; na.rho_last = L.rho_last; na.off = L.off; na.members = L.members;
+    na.taken = L.taken; na.keep = L.keep; na.gdist = gdist; na.info = L.info; na.selected_idx = selected_idx;
+    n3_niche_kernel<<<1, 1024, 0, s>>>(na);
+    EVOXB_LAUNCH_CHECK("n3_niche_kernel");
+    if (norm_out) EVOXB_CUDA(cudaMemcpyAsync(norm_out, L.norm, sizeof(float) * 3 * (size_t)m, cudaMemcpyDeviceToDevice, s));
+    if (next_key) {  // keys[0] of jax.random.split(key, pop_size + 1), nsga3.py:154, :209
+        next_key[0] = jax_split_word(key[0], key[1], (uint32_t)pop_size + 1u, 0u);
+        next_key[1] = jax_split_word(key[0], key[1], (uint32_t)pop_size + 1u, 1u);
+    }
+    prof.mark("end", s);
     return 0;
 }
 

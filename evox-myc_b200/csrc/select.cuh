@@ -17,7 +17,10 @@ namespace evoxb {
 
 __global__ void rank_hist_kernel(const int *__restrict__ rank, int64_t n, int *__restrict__ hist) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i < n) atomicAdd(hist + rank[i], 1);
+    if (i < n) {
+        const int r = rank[i];
+        if ((unsigned)r < (unsigned)n) atomicAdd(hist + r, 1);  // ranks outside [0, n) (a failed sharded call: -1) are skipped
+    }
 }
 
 // One CTA: smallest r with hist[0] + ... + hist[r] > k  (the value of the k-th smallest rank, 0-based).

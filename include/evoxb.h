@@ -149,6 +149,25 @@ EVOXB_API int evoxb_dtlz2_f32(const float *x, int64_t n, int d, int m, float *f,
 EVOXB_API int evoxb_lsmop1_f32(const float *x, int64_t n, int d, int m, const int32_t *sublen, const int32_t *start,
                                float *f, evoxb_stream_t stream);
 
+/* ---- f3: NSGA-III environmental selection: all of NSGA3.tell after the concatenation
+ * (src/evox/algorithms/mo/nsga3.py:96-211): ranking, last_rank, normalisation by the hyperplane intercepts (or
+ * the worst point when the extreme points are rank deficient), association of every kept row with its nearest
+ * reference direction (ref: (r, m), e.g. UniformSampling, src/evox/operators/sampling/uniform.py:10-60) and the
+ * niche-preserving select loop.  key = the two words of the JAX PRNG key in state.key; the loop draws with
+ * jax.random.randint(keys[selected_number], (), 0, rho_last[group]) of keys = jax.random.split(key, pop_size + 1)
+ * (threefry, JAX 0.4.x layout) and next_key (host, optional) receives keys[0] (:209).
+ *   selected_idx   : out, device (pop_size) int32, ascending row indices of the survivors (:203-205)
+ *   rank_out       : optional out, device (n) int32
+ *   group_id_out   : optional out, device (n) int32, nearest direction (r = none, :141)
+ *   group_dist_out : optional out, device (n) float32 (NaN = none)
+ *   norm_out       : optional out, device (3 m) float32: ideal point, nadir point, extreme row indices
+ * m <= 16.  Stream-ordered; nothing is allocated; host arguments (key, next_key) are read / written at call time. */
+EVOXB_API int evoxb_nsga3_select_workspace_bytes(int64_t n, int m, int64_t r, size_t *bytes);
+EVOXB_API int evoxb_nsga3_select_f32(const float *fitness, int64_t n, int m, int64_t pop_size, const float *ref, int64_t r,
+                                     const uint32_t key[2], int32_t *selected_idx, uint32_t next_key[2], int32_t *rank_out,
+                                     int32_t *group_id_out, float *group_dist_out, float *norm_out, void *ws,
+                                     size_t ws_bytes, evoxb_stream_t stream);
+
 /* ---- e: multi-GPU ranking, one process per GPU (no counterpart in the reference, whose tell() is
  * replicated on every device: src/evox/workflows/std_workflow.py:194, :341) ---------------------------
  * The bit-packed dominance matrix is sharded by COLUMN chunk (4096 dominated individuals per chunk,

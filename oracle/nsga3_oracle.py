@@ -59,7 +59,9 @@ def normalise(fit: np.ndarray, rank: np.ndarray, last_rank: int):
             scal = np.nanmax((ranked / weight[i]).astype(F32), axis=1)  # all-NaN rows stay NaN
             extreme_ind[i] = np.nanargmin(scal)
         extreme = ranked[extreme_ind]
-        full_rank = np.linalg.matrix_rank(extreme) == m
+        # jnp.linalg.matrix_rank of a matrix holding inf / NaN yields NaN singular values, `S > tol` is False
+        # everywhere and the rank is 0 (NumPy raises instead): the worst-point branch is taken
+        full_rank = bool(np.all(np.isfinite(extreme))) and np.linalg.matrix_rank(extreme) == m
         if full_rank:
             plane = np.linalg.solve(extreme, np.ones(m, dtype=F32)).astype(F32)
             nadir = (F32(1) / plane).astype(F32)
