@@ -408,8 +408,10 @@ def run_gpu_arm(args, n, m, desc):
                       "ms_per_launch": build_ms, "pairs_per_s": pairs_rank / (build_ms * 1e-3)})
 
     nsga2_info = None
+    nsga3_info = None
     if world == 1 and not args.no_nsga2:
         nsga2_info = bench_nsga2(args, dev)
+        nsga3_info = bench_nsga3(args, dev)
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -445,6 +447,7 @@ def run_gpu_arm(args, n, m, desc):
         "stages_ms": {k: round(v, 4) for k, v in stages.items()},
         "cpu_baseline": cpu,
         "nsga2": nsga2_info,
+        "nsga3": nsga3_info,
     }
     print(json.dumps(line), flush=True)
     if dist is not None:
@@ -506,6 +509,50 @@ def bench_nsga2(args, dev):
     except Exception as ex:  # pragma: no cover
         out["cpu_port"] = {"error": repr(ex)}
     return out
+
+
+def bench_nsga3(args, dev):
+    """BASELINE configs[4]: NSGA-III on LSMOP1, M = 10, pop = 32768, d = 1000 -- generations/s with ask (SBX +
+    polynomial mutation + clip), LSMOP1 evaluate and the whole tell (ranking, normalisation, association with
+    29315 reference directions, niche selection) as native kernels; stage times of one tell beside it."""
+    import torch
+
+    from evox_myc_b200 import _lib, nsga2, nsga3
+
+    pop, m, d = 32768, 10, 1000
+    lb = np.zeros(d, np.float32)
+    ub = np.concatenate([np.ones(m - 1), 10 * np.ones(d - m + 1)]).astype(np.float32)  # the box of tests/test_lsmop.py:10-14
+    algo = nsga3.NSGA3(lb, ub, m, pop, device=dev)
+    prob = nsga2.LSMOP1(d=d, m=m)
+    state = algo.setup(0)
+    x, state = algo.init_ask(state)
+    f, _ = prob.evaluate(None, x)
+    state = algo.init_tell(state, f)
+
+    def gen(state):
+        x, state = algo.ask(state)
+        f, _ = prob.evaluate(None, x)
+        return algo.tell(state, f)
+
+    for _ in range(3):
+        state = gen(state)
+    gens = max(min(args.steps, 20), 5)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(gens):
+        state = gen(state)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / gens
+    _lib.profile_enable(True)
+    state = gen(state)
+    stages = _lib.profile_read()
+    _lib.profile_enable(False)
+    return {"config": "BASELINE configs[4]: NSGA-III on LSMOP1, M=10, pop=32768, d=1000, 29315 reference points",
+            "generations": gens, "ms_per_generation": ms, "gens_per_s": 1e3 / ms,
+            "tell_stages_ms": {k: round(v, 4) for k, v in stages.items()},
+            "note": "ask / evaluate / tell all native kernels; tell consumes the JAX-layout threefry key like the reference"}
 
 
 def main():
