@@ -1267,17 +1267,18 @@ EVOXB_API int evoxb_nsga3_select_f32(const float *fitness, int64_t n, int m, int
     EVOXB_LAUNCH_CHECK("n3_extreme_kernel");
     n3_nadir_kernel<<<1, 32, 0, s>>>(fitness, m, L.ideal_key, L.ext_key, L.worst_key, L.norm, L.info);
     EVOXB_LAUNCH_CHECK("n3_nadir_kernel");
-    n3_unit_rows_kernel<<<gb, 256, 0, s>>>(fitness, rank, nn, m, L.info, L.norm, L.xu, L.xnorm);
+    int *gid = group_id_out ? group_id_out : L.gid;
+    float *gdist = group_dist_out ? group_dist_out : L.gdist;
+    n3_unit_rows_kernel<<<gb, 256, 0, s>>>(fitness, rank, nn, m, L.info, L.norm, L.xu, L.xnorm, L.kept_list, gid, gdist, rr);
     EVOXB_LAUNCH_CHECK("n3_unit_rows_kernel");
     n3_unit_refs_kernel<<<(unsigned)div_up(r, 256), 256, 0, s>>>(ref, rr, m, L.yu);
     EVOXB_LAUNCH_CHECK("n3_unit_refs_kernel");
 
     prof.mark("nsga3_associate", s);
-    int *gid = group_id_out ? group_id_out : L.gid;
-    float *gdist = group_dist_out ? group_dist_out : L.gdist;
+    const unsigned ga = (unsigned)div_up(n, kN3RowsPerCta);
 #define EVOXB_N3_CASE(MM)                                                                          \
     case MM:                                                                                       \
-        n3_associate_kernel<MM><<<gb, 256, 0, s>>>(L.xu, L.xnorm, nn, L.yu, rr, gid, gdist);      \
+        n3_associate_kernel<MM><<<ga, 256, 0, s>>>(L.xu, L.xnorm, L.kept_list, L.info, L.yu, rr, gid, gdist); \
         break;
     switch (m) {
         EVOXB_N3_CASE(1) EVOXB_N3_CASE(2) EVOXB_N3_CASE(3) EVOXB_N3_CASE(4) EVOXB_N3_CASE(5) EVOXB_N3_CASE(6)

@@ -82,7 +82,8 @@ __host__ __device__ inline uint32_t jax_randint(uint32_t k0, uint32_t k1, uint32
 
 struct Nsga3Layout {
     int *hist;            // [n] rank histogram
-    int *info;            // [64]: [0] last_rank, [1] full-rank flag, [2] rounds of the niche loop
+    int *kept_list;       // [n] rows with rank <= last_rank, any order
+    int *info;            // [64]: [0] last_rank, [1] full-rank flag, [2] rounds of the niche loop, [3] rows kept
     uint32_t *ideal_key;  // [m]
     uint32_t *worst_key;  // [m]
     unsigned long long *ext_key;  // [m] (key of the scalarised value << 32) | row
@@ -107,6 +108,7 @@ inline Nsga3Layout nsga3_layout(void *ws, int64_t n, int m, int64_t r) {
     Carver c(ws);
     const size_t n1 = (size_t)(n > 0 ? n : 1), r1 = (size_t)(r > 0 ? r : 1);
     L.hist = c.take<int>(n1);
+    L.kept_list = c.take<int>(n1);
     L.info = c.take<int>(64);
     L.ideal_key = c.take<uint32_t>((size_t)m);
     L.worst_key = c.take<uint32_t>((size_t)m);
@@ -267,14 +269,24 @@ __global__ void n3_nadir_kernel(const float *__restrict__ f, int m, const uint32
 
 // ---- nsga3.py:133-134 (row side): normalised rows as unit vectors + their norms; unit reference directions ----
 __global__ void __launch_bounds__(256)
-n3_unit_rows_kernel(const float *__restrict__ f, const int *__restrict__ rank, int n, int m, const int *__restrict__ info,
-                    const float *__restrict__ norm, float *__restrict__ xu, float *__restrict__ xnorm) {
+n3_unit_rows_kernel(const float *__restrict__ f, const int *__restrict__ rank, int n, int m, int *__restrict__ info,
+                    const float *__restrict__ norm, float *__restrict__ xu, float *__restrict__ xnorm, int *__restrict__ kept_list,
+                    int *__restrict__ gid, float *__restrict__ gdist, int r) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool kept = i < n && rank[i] <= info[0];
+    // rows that are kept go to a dense list (any order): the association kernel only runs over those
+    const uint32_t bal = __ballot_sync(0xffffffffu, kept);
+    int base = 0;
+    if ((threadIdx.x & 31) == 0 && bal) base = atomicAdd(info + 3, __popc(bal));
+    base = __shfl_sync(0xffffffffu, base, 0);
     if (i >= n) return;
-    if (rank[i] > info[0]) {
+    if (!kept) {
         xnorm[i] = __int_as_float(0x7fc00000);
+        gid[i] = r;  // no direction (nsga3.py:141), distance NaN
+        gdist[i] = __int_as_float(0x7fc00000);
         return;
     }
+    kept_list[base + __popc(bal & ((1u << (threadIdx.x & 31)) - 1u))] = i;
     float v[EVOXB_MAX_OBJECTIVES];
     float s = 0.0f;
 #pragma unroll 1
@@ -299,50 +311,114 @@ n3_unit_refs_kernel(const float *__restrict__ ref, int r, int m, float *__restri
 }
 
 // ---- nsga3.py:134-142: perpendicular distance to every direction, nearest one (NaN skipped, first on ties) ----
+// Eight threads share two kept rows: thread s of the eight takes the directions j = s (mod 8) of every tile (a
+// direction read from shared memory serves both rows), and the eight partial (distance, index) minima are merged
+// by shuffles, the smaller index winning among equal distances.  Directions are staged as float4-padded records
+// (a record is ceil(M / 4) 16-byte loads, conflict-free for the eight records a warp reads at once); the dot
+// product runs k = 0 .. M-1 in one FMA chain.
 template <int M>
 struct N3Tile {
-    static constexpr int value = M <= 8 ? 1024 : 512;  // directions per shared-memory tile (<= 32 KB of floats)
+    static constexpr int kPad = (M + 3) / 4 * 4;
+    static constexpr int value = 8192 / kPad;  // directions per shared-memory tile (32 KB of floats)
 };
+constexpr int kN3Rows = 2;                            // rows per thread group
+constexpr int kN3Split = 8;                           // threads per group (slices of the directions)
+constexpr int kN3RowsPerCta = 256 / kN3Split * kN3Rows;  // 64
 
 template <int M>
 __global__ void __launch_bounds__(256)
-n3_associate_kernel(const float *__restrict__ xu, const float *__restrict__ xnorm, int n, const float *__restrict__ yu, int r,
-                    int *__restrict__ gid, float *__restrict__ gdist) {
-    constexpr int kN3RefTile = N3Tile<M>::value;
-    __shared__ float ys[kN3RefTile * M];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const float nn = i < n ? xnorm[i] : __int_as_float(0x7fc00000);
-    const bool kept = nn == nn;  // rows beyond the last front carry a NaN norm; a zero row gives NaN unit vectors below
-    float x[M];
+n3_associate_kernel(const float *__restrict__ xu, const float *__restrict__ xnorm, const int *__restrict__ kept_list,
+                    const int *__restrict__ info, const float *__restrict__ yu, int r, int *__restrict__ gid,
+                    float *__restrict__ gdist) {
+    constexpr int kPad = N3Tile<M>::kPad, kTile = N3Tile<M>::value;
+    __shared__ __align__(16) float ys[kTile * kPad];
+    const int nkept = info[3];
+    if ((int)(blockIdx.x * kN3RowsPerCta) >= nkept) return;  // uniform over the CTA
+    const int slice = threadIdx.x & (kN3Split - 1), group = threadIdx.x / kN3Split;
+    int row[kN3Rows];
+    float nn[kN3Rows], x[kN3Rows][kPad], best[kN3Rows];
+    int arg[kN3Rows];
+    bool some[kN3Rows], ok[kN3Rows];
+    float sthr[kN3Rows];
 #pragma unroll
-    for (int k = 0; k < M; ++k) x[k] = kept ? xu[(int64_t)i * M + k] : 0.0f;
-    float best = __int_as_float(0x7f800000);
-    int arg = -1;
-    bool some = false;  // a distance that is not NaN was seen
-    for (int j0 = 0; j0 < r; j0 += kN3RefTile) {
-        const int jn = min(kN3RefTile, r - j0);
-        __syncthreads();
-        for (int q = threadIdx.x; q < jn * M; q += 256) ys[q] = yu[(int64_t)j0 * M + q];
-        __syncthreads();
-        if (!__any_sync(0xffffffffu, kept)) continue;
-        for (int j = 0; j < jn; ++j) {
-            float c = 0.0f;
+    for (int q = 0; q < kN3Rows; ++q) {
+        const int slot = blockIdx.x * kN3RowsPerCta + group * kN3Rows + q;
+        row[q] = slot < nkept ? kept_list[slot] : -1;
+        nn[q] = row[q] >= 0 ? xnorm[row[q]] : __int_as_float(0x7fc00000);
 #pragma unroll
-            for (int k = 0; k < M; ++k) c = fmaf(x[k], ys[j * M + k], c);
-            const float d = nn * sqrtf(1.0f - c * c);
-            some = some || (d == d);
-            if (d < best) {  // NaN compares false: skipped; strict: the first of equal distances stays
-                best = d;
-                arg = j0 + j;
+        for (int k = 0; k < kPad; ++k) x[q][k] = (row[q] >= 0 && k < M) ? xu[(int64_t)row[q] * M + k] : 0.0f;
+        best[q] = __int_as_float(0x7f800000);
+        arg[q] = -1;
+        some[q] = false;
+        ok[q] = nn[q] > 0.0f && nn[q] < __int_as_float(0x7f800000);
+        sthr[q] = __int_as_float(0x7f800000);
+    }
+    for (int j0 = 0; j0 < r; j0 += kTile) {
+        const int jn = min(kTile, r - j0);
+        __syncthreads();
+        for (int q = threadIdx.x; q < jn * kPad; q += 256) {
+            const int j = q / kPad, k = q - j * kPad;
+            ys[q] = k < M ? yu[(int64_t)(j0 + j) * M + k] : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int j = slice; j < jn; j += kN3Split) {
+            float y[kPad];
+#pragma unroll
+            for (int k4 = 0; k4 < kPad / 4; ++k4) {
+                const float4 t = *reinterpret_cast<const float4 *>(ys + j * kPad + 4 * k4);
+                y[4 * k4] = t.x; y[4 * k4 + 1] = t.y; y[4 * k4 + 2] = t.z; y[4 * k4 + 3] = t.w;
+            }
+#pragma unroll
+            for (int q = 0; q < kN3Rows; ++q) {
+                float c = 0.0f;
+#pragma unroll
+                for (int k = 0; k < M; ++k) c = fmaf(x[q][k], y[k], c);
+                // d = |x| sqrt(1 - cos^2), compared exactly like the reference -- but the square root is only taken
+                // when 1 - cos^2 is small enough to matter: sthr bounds from above every value whose distance could
+                // still be <= the best one (two roundings of <= 2^-24 each separate d from |x| sqrt(s))
+                const float sq = __fsub_rn(1.0f, __fmul_rn(c, c));
+                if (ok[q]) {
+                    some[q] = some[q] || (sq >= 0.0f);
+                    if (sq <= sthr[q]) {
+                        const float d = nn[q] * sqrtf(sq);
+                        if (d < best[q]) {  // NaN compares false: skipped; strict: the first of equal distances stays
+                            best[q] = d;
+                            arg[q] = j0 + j;
+                            sthr[q] = sq * (1.0f + 1e-6f);
+                        }
+                    }
+                } else {  // |x| is 0, inf or NaN: no short cut
+                    const float d = nn[q] * sqrtf(sq);
+                    some[q] = some[q] || (d == d);
+                    if (d < best[q]) {
+                        best[q] = d;
+                        arg[q] = j0 + j;
+                    }
+                }
             }
         }
     }
-    if (i < n) {
+#pragma unroll
+    for (int q = 0; q < kN3Rows; ++q) {
+        // merge the eight slices: smaller distance, then smaller direction index (NaN never entered `best`)
+#pragma unroll
+        for (int o = 1; o < kN3Split; o <<= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best[q], o);
+            const int oa = __shfl_xor_sync(0xffffffffu, arg[q], o);
+            const bool os = __shfl_xor_sync(0xffffffffu, some[q] ? 1 : 0, o) != 0;
+            if (oa >= 0 && (arg[q] < 0 || ob < best[q] || (ob == best[q] && oa < arg[q]))) {
+                best[q] = ob;
+                arg[q] = oa;
+            }
+            some[q] = some[q] || os;
+        }
+        if (row[q] < 0 || slice != 0) continue;
         // nanargmin reads NaN as +inf: a row whose distances are +inf or NaN (but not all NaN) gets direction 0 and
         // distance +inf; all NaN -> -1 -> len(ref) (nsga3.py:140-142)
-        if (kept && arg < 0 && some) arg = 0;
-        gid[i] = (kept && arg >= 0) ? arg : r;
-        gdist[i] = (kept && arg >= 0) ? best : __int_as_float(0x7fc00000);
+        if (arg[q] < 0 && some[q]) arg[q] = 0;
+        gid[row[q]] = arg[q] >= 0 ? arg[q] : r;
+        gdist[row[q]] = arg[q] >= 0 ? best[q] : __int_as_float(0x7fc00000);
     }
 }
 
