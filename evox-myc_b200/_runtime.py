@@ -23,11 +23,15 @@ def require_cuda() -> None:
 
 
 def workspace(nbytes: int, device: torch.device, slot: str = "main") -> torch.Tensor:
-    """Grow-only per-thread, per-device scratch buffer (256-byte aligned by the caching allocator)."""
+    """Grow-only scratch buffer per (thread, device, CUDA stream) -- 256-byte aligned by the caching allocator.
+    Keyed by the current stream because calls issued under different ``torch.cuda.stream`` contexts overlap on
+    the GPU and must not share the dominance matrix; a buffer that is outgrown goes back to the allocator,
+    which keeps it tied to the stream it was allocated on."""
     cache = getattr(_tls, "ws", None)
     if cache is None:
         cache = _tls.ws = {}
-    key = (device.index if device.index is not None else torch.cuda.current_device(), slot)
+    dev_index = device.index if device.index is not None else torch.cuda.current_device()
+    key = (dev_index, torch.cuda.current_stream(device).cuda_stream, slot)
     buf = cache.get(key)
     if buf is None or buf.numel() < nbytes:
         cache.pop(key, None)

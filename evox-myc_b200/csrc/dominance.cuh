@@ -160,12 +160,10 @@ inline int launch_dominance_build(const float *xt, int64_t npad, int64_t row0, i
         EVOXB_BUILD_CASE(12)
         default: {
             const size_t smem = sizeof(float) * (size_t)(kTileRows + kTileCols) * (size_t)m;
-            static thread_local size_t configured = 0;
-            if (smem > 48 * 1024 && smem > configured) {
+            // the attribute is per device and the call is cheap: set it whenever more than the default is needed
+            if (smem > 48 * 1024)
                 EVOXB_CUDA(cudaFuncSetAttribute(dominance_build_generic_kernel,
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                configured = smem;
-            }
             dominance_build_generic_kernel<<<grid, kBuildThreads, smem, s>>>(xt, npad, n_rows, row0, m, D, row_words);
         }
     }

@@ -86,7 +86,11 @@ EVOXB_API int evoxb_crowding_f32(const float *fitness, const uint8_t *mask, int6
  *     EVOXB_E_WORKSPACE and a message naming both numbers; nothing is launched.
  *   - The first call on each device looks up the array's device address (with that device
  *     current); make that first call before starting any stream capture on the device.
- *   - Every GPU that loads the library holds the 8 MiB until the process exits.
+ *   - Every GPU that loads the library holds the 8 MiB until the process exits.  The driver reserves
+ *     them when the library's module is first loaded on a device (with CUDA's lazy loading that is the
+ *     first call into the library on that device, possibly this one), so on a device whose memory is
+ *     already exhausted that first call can itself fail with EVOXB_E_CUDA: make one warm-up call per
+ *     device while memory is still available.
  *   - All calls on a device share the one array and it keeps the previous call's contents; each
  *     call writes everything it later reads, so nothing needs clearing -- but two calls that
  *     overlap on the GPU (different streams, or different host threads on the same device)
