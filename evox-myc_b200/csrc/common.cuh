@@ -55,6 +55,37 @@ struct ChunkMap {
     __host__ __device__ int global(int lc) const { return first + lc * stride; }
 };
 
+// Where the packed row of individual i starts.  Two layouts of the bit matrix:
+//   rectangular (unsorted full matrix, m > 16): row i = row_vec uint4 starting at i * row_vec;
+//   triangular  (presorted population): row i only has bits in the column chunks at or after its own chunk
+//     a = i / 4096, and only those LOCAL chunks are stored (this GPU owns chunks first, first + stride, ...):
+//     nl(a) * 32 uint4 per row of chunk a.  vstart() is the row's "virtual start" -- where it would begin if the
+//     local chunks in front of its own were stored too -- so that the uint4 of local chunk lc sits at
+//     vstart(i) + lc * 32 in both layouts.  Halves the matrix (N^2/16 bytes on one GPU).
+// Pure arithmetic (no table to load before a tile can be addressed): with before(a) = number of local chunks in
+// front of chunk a, the rows of chunks < a hold 4096 * 32 * (a * nlocal - sum_{a' < a} before(a')) uint4.
+struct TriRows {
+    int64_t row_vec;  // rectangular layout: uint4 per row
+    int64_t row_words;  // the same in 32-bit words
+    int tri;          // 1 = triangular storage
+    int first, stride, nlocal;
+    __host__ __device__ __forceinline__ int before(int a) const { return a <= first ? 0 : (a - first - 1) / stride + 1; }
+    __host__ __device__ __forceinline__ int row_uint4(int a) const { return tri ? (nlocal - before(a)) * 32 : (int)row_vec; }
+    // uint4 stored in front of the rows of chunk a
+    __host__ __device__ __forceinline__ int64_t chunk_base(int a) const {
+        const int64_t T = a - 1 - first > 0 ? a - 1 - first : 0;  // chunks first + 1 .. a - 1 have a local chunk in front
+        const int64_t Q = T / stride, R = T - Q * stride;
+        const int64_t g = T + stride * (Q * (Q - 1) / 2) + Q * R;  // sum of before(a') over a' < a
+        return 4096ll * 32ll * ((int64_t)a * nlocal - g);
+    }
+    __host__ __device__ __forceinline__ int64_t vstart(int64_t i) const {
+        if (!tri) return i * row_vec;
+        const int a = (int)(i >> 12);
+        const int bf = before(a);
+        return chunk_base(a) + (i & 4095) * (int64_t)((nlocal - bf) * 32) - (int64_t)bf * 32;
+    }
+};
+
 // Bump allocator over the caller's workspace; every block is 256-byte aligned.
 struct Carver {
     char *base;

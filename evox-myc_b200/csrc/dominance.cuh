@@ -203,11 +203,12 @@ inline TriGrid make_tri_grid(int64_t npad, int64_t n_rows) {
     return g;
 }
 
-template <int M>
+// kPacked: triangular storage (TriRows::vstart); the rectangular instance keeps the plain row * stride addressing
+template <int M, bool kPacked>
 __global__ void __launch_bounds__(kBuildThreads)
 dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows, const int *__restrict__ uid_row,
                            const int *__restrict__ uid_col, const float *__restrict__ tile_min1,
-                           const float *__restrict__ tile_max1, uint32_t *__restrict__ D, int64_t row_words, TriGrid g) {
+                           const float *__restrict__ tile_max1, uint32_t *__restrict__ D, TriRows rows, TriGrid g) {
     constexpr int K = (M > 1) ? (M - 1) : 1;  // objectives 1..M-1 are compared
     __shared__ float xs[kTileRows][K];
     __shared__ int us[kTileRows];
@@ -244,7 +245,6 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
     const int64_t tile_col0 = (int64_t)ct * kTileCols;
     const int64_t col_base = tile_col0 + warp * (kC * 32);
     const int64_t word_base = word0 + warp * kC;
-
     // Tile-level test on objective 1 (rows inside a chunk are ordered by it, so a 1024-tile is a band of
     // x_1; presort.cuh): if every row's x_1 exceeds every column's, nothing in the tile can dominate.
     // (A column tile of the rows' own chunk may lie "left" of the rows: inside a chunk positions carry no
@@ -257,7 +257,7 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
         if (r_lo > c_hi) {
             for (int rb = 0; rb < kTileRows; rb += 32) {
                 const int64_t r = tile_row0 + rb + lane;
-                if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = make_uint4(0u, 0u, 0u, 0u);
+                if (r < n_rows) *reinterpret_cast<uint4 *>((kPacked ? D + rows.vstart(r) * 4 + word_base : D + r * rows.row_words + word_base)) = make_uint4(0u, 0u, 0u, 0u);
             }
             return;
         }
@@ -368,7 +368,7 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
             }
         }
         const int64_t r = tile_row0 + rb + lane;
-        if (r < n_rows) *reinterpret_cast<uint4 *>(D + r * row_words + word_base) = v;
+        if (r < n_rows) *reinterpret_cast<uint4 *>((kPacked ? D + rows.vstart(r) * 4 + word_base : D + r * rows.row_words + word_base)) = v;
     }
 #undef EVOXB_TRI_BLOCK
 }
@@ -377,7 +377,7 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
 // matrix row holds cm->nlocal * 128 words.
 inline int launch_dominance_build_tri(const float *xt, int64_t npad, int64_t n_rows, int m, const int *uid_row,
                                       const int *uid_col, const float *tile_min1, const float *tile_max1, uint32_t *D,
-                                      int64_t row_words, cudaStream_t s, const ChunkMap *cm = nullptr) {
+                                      TriRows rows, cudaStream_t s, const ChunkMap *cm = nullptr) {
     if (n_rows <= 0) return 0;
     TriGrid g = make_tri_grid(npad, n_rows);
     if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
@@ -389,10 +389,14 @@ inline int launch_dominance_build_tri(const float *xt, int64_t npad, int64_t n_r
         if (g.nrt > 65535) return fail(EVOXB_E_UNSUPPORTED, "too many row tiles (%d)", g.nrt);
         grid = dim3((unsigned)(cm->nlocal * 4), (unsigned)g.nrt);
     }
-#define EVOXB_TRI_CASE(MM)                                                                                     \
-    case MM:                                                                                                   \
-        dominance_build_tri_kernel<MM><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, uid_row, uid_col,      \
-                                                                      tile_min1, tile_max1, D, row_words, g);  \
+#define EVOXB_TRI_CASE(MM)                                                                                         \
+    case MM:                                                                                                       \
+        if (rows.tri)                                                                                              \
+            dominance_build_tri_kernel<MM, true><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, uid_row, uid_col, \
+                                                                                tile_min1, tile_max1, D, rows, g);  \
+        else                                                                                                       \
+            dominance_build_tri_kernel<MM, false><<<grid, kBuildThreads, 0, s>>>(xt, npad, n_rows, uid_row, uid_col, \
+                                                                                 tile_min1, tile_max1, D, rows, g); \
         break;
     switch (m) {
         EVOXB_TRI_CASE(1) EVOXB_TRI_CASE(2) EVOXB_TRI_CASE(3) EVOXB_TRI_CASE(4) EVOXB_TRI_CASE(5) EVOXB_TRI_CASE(6)

@@ -49,7 +49,9 @@ struct evoxb_comm {
 namespace evoxb {
 
 struct NdsLayout {
-    int64_t n, npad, row_words;
+    int64_t n, npad, row_words;  // row_words: words per row of the rectangular layout (also the triangle's widest row)
+    int64_t d_words;             // words of the bit matrix as stored
+    bool packed;                 // triangular storage (TriRows): only for populations whose rectangle is too big
     int m, nchunks;
     bool tri;  // presorted population, upper-triangular matrix (m <= 16); otherwise full matrix in input order
     float *xt;
@@ -80,6 +82,7 @@ struct NdsLayout {
 };
 
 static bool nds_use_tri(int m) { return m <= 16; }
+
 
 constexpr int kFrontBatch = 4;  // fronts enqueued between two host checks of "front empty?" (multi-GPU)
 
@@ -122,7 +125,19 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         L.cnt = c.take<int>(kMaxChunks);
     }
     L.flow_ring = c.take<unsigned char>(flow_ring_bytes(L.npad / 32));
-    L.D = c.take<uint32_t>((size_t)n_rows * (size_t)L.row_words);
+    // Only the triangle of the presorted matrix is ever written or read.  Storing just that (TriRows) halves
+    // the workspace, but measured on the B200 it costs time: the build kernel's stores are 8-10 % slower with
+    // the dense rows (c4: 4.38 -> 4.8 ms) and the variable row stride adds address arithmetic to every staged
+    // row of count / peel.  So the rectangle (row stride = a power of two) stays the layout up to N = 262144
+    // (8 GiB per GPU of 180) and the triangle is used beyond, where memory starts to matter more than 7 %.
+    L.packed = L.tri && L.npad > 262144;
+    if (L.packed) {
+        const TriRows tr{L.row_words >> 2, L.row_words, 1, L.cm.first, L.cm.stride, L.cm.nlocal};
+        L.d_words = n_rows > 0 ? tr.chunk_base(L.nchunks) * 4 : 0;
+    } else {
+        L.d_words = n_rows * L.row_words;
+    }
+    L.D = c.take<uint32_t>((size_t)L.d_words);
     L.bytes = c.total();
     return L;
 }
@@ -172,6 +187,10 @@ static int coop_blocks(const void *kern, int threads, int cap_per_sm, int *block
 
 
 namespace evoxb {
+
+static TriRows make_rows(const NdsLayout &L) {
+    return TriRows{L.row_words >> 2, L.row_words, L.packed ? 1 : 0, L.cm.first, L.cm.stride, L.cm.nlocal};
+}
 
 // ---- data-flow peel (peel_flow.cuh): launch configuration ------------------------------------------
 // Which peel runs: "flow" = peel_flow_kernel wherever it is applicable, "grid" = the cooperative-grid
@@ -269,7 +288,7 @@ static int run_peel_flow(const NdsLayout &L, int64_t n, int32_t *rank, const int
                          cudaStream_t s) {
     FlowArgs a{};
     a.D = L.D;
-    a.row_words = L.row_words;
+    a.rows = make_rows(L);
     a.nchunks = L.nchunks;
     a.n = (int)n;
     a.tri = L.tri ? 1 : 0;
@@ -354,7 +373,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         if (int rc = run_presort(fitness, n, m, L, s)) return rc;
         perm = L.perm;
         prof.mark("dominance_build", s);
-        if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, L.row_words, s)) return rc;
+        if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, make_rows(L), s)) return rc;
     } else {
         transpose_pad_kernel<<<(unsigned)div_up(L.npad, 256), 256, 0, s>>>(fitness, n, m, L.npad, L.xt);
         EVOXB_LAUNCH_CHECK("transpose_pad_kernel");
@@ -376,7 +395,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
 
     prof.mark("dominator_count", s);
     const TileBands tb{L.tri ? L.tile_min1 : nullptr, L.tri ? L.tile_max1 : nullptr};
-    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, tri, ChunkMap{0, 1, L.nchunks},
+    dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, make_rows(L), L.nchunks, n, tri, ChunkMap{0, 1, L.nchunks},
                                                            L.count, tb);
     EVOXB_LAUNCH_CHECK("dominator_count_kernel");
 
@@ -401,7 +420,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     }
     {
         const uint32_t *D = L.D;
-        int64_t row_words = L.row_words;
+        TriRows row_words = make_rows(L);
         int nchunks = L.nchunks;
         int nn = (int)n;
         int tri_arg = tri;
@@ -492,7 +511,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
     if (int rc = run_presort(fitness, n, m, L, s)) return rc;
 
     prof.mark("dominance_build", s);
-    if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, L.row_words, s, &L.cm)) return rc;
+    if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, make_rows(L), s, &L.cm)) return rc;
 
     const void *p2p_kern = L.nchunks <= 32    ? (const void *)peel_p2p_kernel<1>
                            : L.nchunks <= 128 ? (const void *)peel_p2p_kernel<4>
@@ -502,7 +521,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
     const TileBands tb{L.tile_min1, L.tile_max1};
     prof.mark("dominator_count", s);
     if (L.cm.nlocal > 0) {
-        dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, n, 1, L.cm, L.count, tb);
+        dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, make_rows(L), L.nchunks, n, 1, L.cm, L.count, tb);
         EVOXB_LAUNCH_CHECK("dominator_count_kernel");
     }
 
@@ -524,7 +543,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         }
         if (all_ok) {
             a.D = L.D;
-            a.row_words = L.row_words;
+            a.rows = make_rows(L);
             a.nchunks = L.nchunks;
             a.n = (int)n;
             a.tri = 1;
@@ -560,7 +579,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         comm->last_path = 1;
         // fused path: one persistent kernel per GPU exchanges the front bitmask over peer memory
         const uint32_t *D = L.D;
-        int64_t row_words = L.row_words;
+        TriRows row_words = make_rows(L);
         int nchunks = L.nchunks, nn = (int)n;
         ChunkMap cm = L.cm;
         int *count = L.count, *rk = rank, *list = L.list, *cnt = L.cnt, *fronts = comm->fronts_dev;
@@ -596,7 +615,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
                                                                   rank, L.perm, L.list, L.cnt, L.totals + b);
             EVOXB_LAUNCH_CHECK("front_expand_kernel");
             if (L.cm.nlocal > 0) {
-                front_subtract_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, L.row_words, L.nchunks, (int)n, 1, L.cm, L.list,
+                front_subtract_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, make_rows(L), L.nchunks, (int)n, 1, L.cm, L.list,
                                                                       L.cnt, L.count, tb);
                 EVOXB_LAUNCH_CHECK("front_subtract_kernel");
             }

@@ -71,7 +71,7 @@ struct PeelSmem {
     union {
         uint32_t fin[kPlanes][kChunkWords];          // CTA totals, plane-major (expansion)
         struct {
-            int rows[kStageRows];                    // row ids of the members being streamed
+            int rows[kStageRows];                    // where the members' packed rows start (TriRows::vstart, in uint4)
             float rowmin[kStageRows];                // smallest x_1 of each such row's 1024-tile
         } st;
     };
@@ -189,13 +189,12 @@ __device__ __forceinline__ int member_row(const int *__restrict__ list, const Pr
 
 // Streams members t0..t1 (region-major numbering) restricted to the 4096-column chunk `chunk` and
 // adds sign * (column sums) to count[].
-__device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_words, const int *__restrict__ list,
+__device__ void accumulate_chunk(const uint32_t *__restrict__ D, TriRows rows, const int *__restrict__ list,
                                  const PrefixSmem &ps, int nregions, int64_t t0, int64_t t1, int local_chunk, int chunk,
                                  int *__restrict__ count, int sign, PeelSmem &sm, TileBands tb) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const uint4 *base = reinterpret_cast<const uint4 *>(D + (int64_t)local_chunk * kChunkWords) + lane;
-    const int64_t row_vec = row_words >> 2;  // row stride in uint4
     // this lane's 128 columns lie in column tile chunk * 4 + lane / 8; +inf = "always fetch"
     const float col_max = tb.tmax ? tb.tmax[chunk * 4 + (lane >> 3)] : __int_as_float(0x7f800000);
 
@@ -212,7 +211,7 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
             // all threads resolve member -> row in parallel (one list-load latency per round)
             for (int q = threadIdx.x; q < gn; q += kPeelThreads) {
                 const int row = member_row(list, ps, nregions, g0 + q);
-                sm.st.rows[q] = row;
+                sm.st.rows[q] = (int)rows.vstart(row);  // < 2^31 uint4 for every matrix that fits in HBM
                 sm.st.rowmin[q] = tb.tmin ? tb.tmin[row >> 10] : 0.0f;
             }
             __syncthreads();
@@ -225,7 +224,7 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
                     // a NaN band (a tile of NaN rows only) compares false and is fetched
                     const int qc = min(qq, gn - 1);
                     const bool fetch = qq < gn && !(sm.st.rowmin[qc] > col_max);
-                    v[b] = ldg_stream_v4_if(base + (int64_t)sm.st.rows[qc] * row_vec, fetch);
+                    v[b] = ldg_stream_v4_if(base + (int64_t)sm.st.rows[qc], fetch);
                 }
                 uint32_t w[kBatch];
 #pragma unroll
@@ -308,7 +307,7 @@ __device__ void accumulate_chunk(const uint32_t *__restrict__ D, int64_t row_wor
 }
 
 // One front (or, with list == nullptr, all rows): the caller has run build_prefix().
-__device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, bool tri, ChunkMap cm,
+__device__ void accumulate_front(const uint32_t *__restrict__ D, TriRows rows, int nchunks, bool tri, ChunkMap cm,
                                  const int *__restrict__ list, const PrefixSmem &ps, int *__restrict__ count, int sign,
                                  PeelSmem &sm, TileBands tb) {
     const long long total = ps.S[cm.nlocal];
@@ -329,7 +328,7 @@ __device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_wor
         const int lc = chunk_order(i, cm.nlocal, tri);
         const int chunk = cm.global(lc);
         if (t1 > t0)
-            accumulate_chunk(D, row_words, list, ps, tri ? chunk + 1 : nchunks, t0, t1, lc, chunk, count, sign, sm, tb);
+            accumulate_chunk(D, rows, list, ps, tri ? chunk + 1 : nchunks, t0, t1, lc, chunk, count, sign, sm, tb);
         s += t1 - t0;
         ++i;
     }
@@ -337,12 +336,12 @@ __device__ void accumulate_front(const uint32_t *__restrict__ D, int64_t row_wor
 
 // K2: count[j] += number of rows in [0, n_rows) that dominate j   (non_dominate.py:61)
 __global__ void __launch_bounds__(kPeelThreads)
-dominator_count_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int64_t n_rows, int tri,
+dominator_count_kernel(const uint32_t *__restrict__ D, TriRows rows, int nchunks, int64_t n_rows, int tri,
                        ChunkMap cm, int *__restrict__ count, TileBands tb) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     build_prefix(nullptr, nchunks, n_rows, tri != 0, cm, ps);
-    accumulate_front(D, row_words, nchunks, tri != 0, cm, nullptr, ps, count, +1, sm, tb);
+    accumulate_front(D, rows, nchunks, tri != 0, cm, nullptr, ps, count, +1, sm, tb);
 }
 
 // Front detection: every j < n with count[j] == 0 joins the front, gets its rank, and drops to -1
@@ -392,7 +391,7 @@ struct PeelCtrl {
 // K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).
 template <int kPer>
 __global__ void __launch_bounds__(kPeelThreads, 2)
-peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri,
+peel_persistent_kernel(const uint32_t *__restrict__ D, TriRows rows, int nchunks, int n, int tri,
                        int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm,
                        int *__restrict__ list, PeelCtrl *__restrict__ ctrl, TileBands tb, int front0_limit) {
     __shared__ PeelSmem sm;
@@ -410,7 +409,7 @@ peel_persistent_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nc
         if (ps.pc[nchunks] == 0) break;  // non_dominate.py:76-78: while any(front)
         if (blockIdx.x == 0)
             for (int c = threadIdx.x; c < nchunks; c += blockDim.x) ctrl->cnt[(r + 1) & 1][c] = 0;
-        accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm, tb);
+        accumulate_front(D, rows, nchunks, tri != 0, cm, list, ps, count, -1, sm, tb);
         grid.sync();
         ++r;
     }
@@ -478,12 +477,12 @@ front_expand_kernel(const uint32_t *__restrict__ gathered, int nranks, int slice
 
 // Subtracts the rows of the current front from this GPU's columns.
 __global__ void __launch_bounds__(kPeelThreads)
-front_subtract_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, int tri, ChunkMap cm,
+front_subtract_kernel(const uint32_t *__restrict__ D, TriRows rows, int nchunks, int n, int tri, ChunkMap cm,
                       const int *__restrict__ list, const int *__restrict__ cnt, int *__restrict__ count, TileBands tb) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
     build_prefix(cnt, nchunks, n, tri != 0, cm, ps);
-    accumulate_front(D, row_words, nchunks, tri != 0, cm, list, ps, count, -1, sm, tb);
+    accumulate_front(D, rows, nchunks, tri != 0, cm, list, ps, count, -1, sm, tb);
 }
 
 // ---- multi-GPU, fused: the front loop and its exchange in ONE persistent kernel per GPU ---------------
@@ -542,7 +541,7 @@ __device__ __forceinline__ unsigned long long global_ns() {
 
 template <int kPer>
 __global__ void __launch_bounds__(kPeelThreads, 2)
-peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, int n, ChunkMap cm,
+peel_p2p_kernel(const uint32_t *__restrict__ D, TriRows rows, int nchunks, int n, ChunkMap cm,
                 int *__restrict__ count, int *__restrict__ rank, const int *__restrict__ perm, int *__restrict__ list,
                 int *__restrict__ cnt, XchgCtx x, int *__restrict__ fronts_done,
                 TileBands tb, unsigned int *host_error, unsigned long long timeout_ns) {
@@ -668,7 +667,7 @@ peel_p2p_kernel(const uint32_t *__restrict__ D, int64_t row_words, int nchunks, 
         // 5. subtract the front's rows from my columns
         build_prefix_t<kPer>(cnt, nchunks, n, true, cm, ps);
         if (ps.pc[nchunks] == 0) break;  // the same bitmask everywhere: every rank stops at the same front
-        accumulate_front(D, row_words, nchunks, true, cm, list, ps, count, -1, sm, tb);
+        accumulate_front(D, rows, nchunks, true, cm, list, ps, count, -1, sm, tb);
         grid.sync();
         ++r;
     }

@@ -138,7 +138,7 @@ struct FlowPeers {
 
 struct FlowArgs {
     const uint32_t *D;
-    int64_t row_words;
+    TriRows rows;         // where packed rows start (rectangular or triangular storage)
     int nchunks, n, tri;
     ChunkMap cm;
     const int *count;     // dominator counts of this GPU's columns, indexed by (sorted) position
@@ -308,7 +308,6 @@ __device__ __forceinline__ void flow_piece_pass(const FlowArgs &a, const FlowPie
         if (ng > max_ng) ng = max_ng;
         lg_ng = 31 - __clz(ng);
         const int rows_per_tile = kFlowTileWords >> lg_w;
-        const int64_t row_vec = a.row_words >> 2;
         const bool tri = a.tri != 0;
         const int part = t & (nparts - 1);
         const uint4 *base = reinterpret_cast<const uint4 *>(a.D + (int64_t)pc.lc * kChunkWords + pc.unit0 * kUnitWords) + part;
@@ -332,7 +331,7 @@ __device__ __forceinline__ void flow_piece_pass(const FlowArgs &a, const FlowPie
                 // rows of later chunks have nothing (and nothing defined) in this chunk's columns; a row tile whose
                 // smallest x_1 exceeds the column tile's largest was zero-filled by the build kernel
                 const bool fetch = i < items && (!tri || (row >> 12) <= pc.chunk) && !(sm.tmin[row >> 10] > col_max);
-                v[u] = ldg_stream_v4_if(base + (int64_t)row * row_vec, fetch);
+                v[u] = ldg_stream_v4_if(base + a.rows.vstart(row), fetch);
             }
         };
         issue(0);

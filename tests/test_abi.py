@@ -40,8 +40,14 @@ def test_argument_validation_without_gpu():
     L = _lib.lib()
     need = ctypes.c_size_t()
     assert L.evoxb_nds_workspace_bytes(262144, 5, ctypes.byref(need)) == 0
-    # the packed matrix dominates: n * n / 8 bytes
+    # the packed matrix dominates: n * n / 8 bytes up to 262144 rows ...
     assert 262144 * 262144 // 8 <= need.value < 262144 * 262144 // 8 + (64 << 20)
+    # ... and only its triangle beyond (row i keeps the chunks from its own on): n^2 / 16 + half a chunk column per row
+    assert L.evoxb_nds_workspace_bytes(524288, 5, ctypes.byref(need)) == 0
+    tri = 524288 * 524288 // 16
+    assert tri <= need.value < tri + 524288 * 4096 // 16 + (128 << 20)
+    assert L.evoxb_nds_workspace_bytes(5000, 20, ctypes.byref(need)) == 0  # m > 16: full matrix in input order
+    assert 5000 * 8192 // 8 <= need.value < 5000 * 8192 // 8 + (8 << 20)
     assert L.evoxb_nds_workspace_bytes(-1, 3, ctypes.byref(need)) == -1
     assert L.evoxb_nds_workspace_bytes(10, 0, ctypes.byref(need)) == -1
     assert L.evoxb_nds_workspace_bytes(10, 33, ctypes.byref(need)) == -1

@@ -209,3 +209,13 @@ def test_deep_front_stress_m2_full_size():
     fin = np.isfinite(w_crowd)
     assert np.array_equal(np.isfinite(crowd), fin)
     np.testing.assert_allclose(crowd[fin], w_crowd[fin], rtol=1e-6, atol=0)
+
+
+def test_triangular_storage_beyond_262144_rows():
+    """Above 262144 rows only the triangle of the bit matrix is stored (row i keeps the chunks from its own on):
+    same ranks, checked at 270000 x 6 against the C oracle (the sharded layout is covered in test_sharded_gpu)."""
+    import evox_myc_b200 as e
+    from oracle import c_oracle
+
+    x = h.uniform(270000, 6, 57)
+    assert np.array_equal(e.non_dominated_sort(x), c_oracle.non_dominated_sort(x))
