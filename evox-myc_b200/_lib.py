@@ -45,6 +45,7 @@ EXPORTS = [
     "evoxb_comm_set_timeout_ms",
     "evoxb_comm_last_path",
     "evoxb_shard_plan",
+    "evoxb_flow_plan",
     "evoxb_nds_sharded_workspace_bytes",
     "evoxb_nds_rank_sharded_f32",
     "evoxb_nsga2_select_sharded_f32",
@@ -102,6 +103,7 @@ def lib() -> ctypes.CDLL:
         L.evoxb_comm_set_timeout_ms.argtypes = [vp, i64]
         L.evoxb_comm_last_path.argtypes = [vp]
         L.evoxb_shard_plan.argtypes = [i64, i32, i32, ip, ip, ip, ip]
+        L.evoxb_flow_plan.argtypes = [i64, i32, i32, i32, i32, ip, ip, ip, ctypes.POINTER(ctypes.c_int32), i32]
         L.evoxb_nds_sharded_workspace_bytes.argtypes = [i64, i32, i32, i32, ctypes.POINTER(sz)]
         L.evoxb_nds_rank_sharded_f32.argtypes = [vp, i64, i32, vp, vp, sz, vp, vp]
         L.evoxb_nsga2_select_sharded_f32.argtypes = [vp, i64, i32, i64, vp, vp, vp, vp, sz, vp, vp]

@@ -1069,6 +1069,33 @@ EVOXB_API int evoxb_shard_plan(int64_t n, int rank, int nranks, int *first_chunk
     return 0;
 }
 
+// Column ownership of the data-flow peel kernel (peel_flow.cuh) for one rank: pure host arithmetic, the same the
+// kernel redoes on the device.  pieces (optional, 4 ints each: cta, chunk, first unit, units) lists every piece.
+EVOXB_API int evoxb_flow_plan(int64_t n, int rank, int nranks, int tri, int max_ctas, int *grid, int *npieces, int *max_words,
+                              int32_t *pieces, int pieces_cap) {
+    if (n < 1 || nranks < 1 || rank < 0 || rank >= nranks || max_ctas < 1) return fail(EVOXB_E_INVALID, "bad arguments");
+    NdsLayout L = nds_layout(nullptr, n, 1, 0, nranks, rank);
+    if (L.nchunks > kFlowMaxChunks) return fail(EVOXB_E_UNSUPPORTED, "n = %lld exceeds the data-flow kernel's %d chunks", (long long)n, kFlowMaxChunks);
+    const FlowPlan p = flow_make_plan(L.nchunks, L.cm, tri != 0, max_ctas);
+    if (grid) *grid = p.grid;
+    if (npieces) *npieces = p.npieces;
+    if (max_words) *max_words = p.max_words;
+    if (pieces && p.grid > 0) {
+        int idx = 0;
+        for (int lc = L.cm.nlocal - 1; lc >= 0; --lc) {
+            const int nu = flow_piece_units(flow_unit_weight(L.cm.global(lc), L.nchunks, tri != 0), p.target);
+            for (int i = 0; i < kUnitsPerChunk / nu; ++i, ++idx) {
+                if (idx >= pieces_cap) return fail(EVOXB_E_INVALID, "pieces_cap too small (%d pieces)", p.npieces);
+                pieces[4 * idx] = idx % p.grid;
+                pieces[4 * idx + 1] = L.cm.global(lc);
+                pieces[4 * idx + 2] = i * nu;
+                pieces[4 * idx + 3] = nu;
+            }
+        }
+    }
+    return 0;
+}
+
 EVOXB_API int evoxb_nds_sharded_workspace_bytes(int64_t n, int m, int rank, int nranks, size_t *bytes) {
     if (!bytes) return fail(EVOXB_E_INVALID, "bytes is null");
     if (int rc = check_common((const void *)1, n, m)) return rc;

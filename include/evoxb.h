@@ -210,6 +210,11 @@ EVOXB_API int evoxb_comm_set_timeout_ms(evoxb_comm_t *comm, int64_t ms);
 EVOXB_API int evoxb_comm_last_path(evoxb_comm_t *comm);
 EVOXB_API int evoxb_shard_plan(int64_t n, int rank, int nranks, int *first_chunk, int *chunk_stride,
                                int *local_chunks, int *total_chunks);
+/* Column ownership of the data-flow peel kernel on `rank` of `nranks` with at most max_ctas CTAs (host arithmetic
+ * only; no counterpart in the reference).  A matrix row is cut in units of 256 columns, a chunk in 1..16 pieces;
+ * pieces (optional) receives 4 ints per piece: owning CTA, global chunk, first unit, number of units.          */
+EVOXB_API int evoxb_flow_plan(int64_t n, int rank, int nranks, int tri, int max_ctas, int *grid, int *npieces,
+                              int *max_words, int32_t *pieces, int pieces_cap);
 EVOXB_API int evoxb_nds_sharded_workspace_bytes(int64_t n, int m, int rank, int nranks, size_t *bytes);
 EVOXB_API int evoxb_nds_rank_sharded_f32(const float *fitness, int64_t n, int m, int32_t *rank, void *ws,
                                          size_t ws_bytes, evoxb_comm_t *comm, evoxb_stream_t stream);

@@ -81,3 +81,39 @@ def test_exchange_protocol_two_gloo_ranks(n, m):
         ok, rounds, fronts = out[r]
         assert ok, f"rank {r}: ranks differ from the oracle"
         assert fronts < rounds <= fronts + 4  # stops within one batch after the first empty front
+
+
+@pytest.mark.parametrize("n", [1, 4097, 32768, 65536, 150001, 262144, 524288])
+@pytest.mark.parametrize("nranks", [1, 2, 3, 8])
+def test_flow_plan_tiles_every_column_once(n, nranks):
+    """Column ownership of the data-flow peel kernel (host arithmetic of csrc/peel_flow.cuh): over all ranks the
+    pieces must cover every 256-column unit of every chunk exactly once, each rank only its own chunks, every CTA
+    at least one piece, and the largest CTA must fit the kernel's shared-memory budget."""
+    import ctypes
+
+    from evox_myc_b200 import _lib
+
+    L = _lib.lib()
+    nchunks = -(-n // 4096)
+    seen = np.zeros((nchunks, 16), dtype=np.int32)
+    for rank in range(nranks):
+        grid, npieces, max_words = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        cap = 16 * nchunks + 16
+        buf = (ctypes.c_int32 * (4 * cap))()
+        _lib.check(L.evoxb_flow_plan(n, rank, nranks, 1, 148, ctypes.byref(grid), ctypes.byref(npieces), ctypes.byref(max_words),
+                                     buf, cap))
+        pieces = np.frombuffer(buf, dtype=np.int32)[: 4 * npieces.value].reshape(-1, 4)
+        own = [c for c in range(nchunks) if c % nranks == rank]
+        if not own:
+            assert grid.value == 0 and npieces.value == 0
+            continue
+        assert 1 <= grid.value <= 148 and grid.value == min(148, npieces.value)
+        assert sorted(set(pieces[:, 0])) == list(range(grid.value))            # no idle CTA among those launched
+        assert set(pieces[:, 1]) == set(own)
+        for cta, chunk, u0, nu in pieces:
+            assert nu in (1, 2, 4, 8, 16) and u0 % nu == 0 and u0 + nu <= 16
+            seen[chunk, u0 : u0 + nu] += 1
+        words = np.bincount(pieces[:, 0], weights=pieces[:, 3] * 8, minlength=grid.value)
+        assert int(words.max()) == max_words.value
+        assert max_words.value * 128 <= 96 * 1024                              # counts of a CTA's columns in shared memory
+    assert np.all(seen == 1)
