@@ -76,6 +76,52 @@ def simulate_exchange(dominates_cols, n: int, rank: int, nranks: int, all_gather
             return ranks, rounds
 
 
+def simulate_flow_exchange(dominates_cols, n: int, rank: int, nranks: int, all_gather, epoch0: int = 0):
+    """The protocol of ``peel_flow_kernel`` across ranks, on host arrays (executable specification, CPU tests).
+
+    Every rank owns the counts of its own column chunks.  Per front it publishes, for each of its 32-column
+    words, the pair ``(word, epoch)`` into one of two buffers chosen by the epoch's parity (here: one
+    ``all_gather`` of the tagged words), reads the COMPLETE bitmask of that front -- every word must carry the
+    current epoch, which is what allows a buffer to be reused two fronts later -- writes the ranks, subtracts the
+    members' rows from its counts, and stops on the first front that is empty everywhere.  Returns the rank
+    vector, the number of fronts and the epoch reached (the next call continues from it).
+    """
+    first, stride, nlocal, nchunks = shard_plan(n, rank, nranks)
+    cols = owned_columns(n, rank, nranks)
+    d = dominates_cols(cols)
+    count = d.sum(axis=0).astype(np.int64)
+    nw = nchunks * (CHUNK // 32)
+    word_of = cols // 32
+    ranks = np.full(n, -1, dtype=np.int32)
+    buffers = np.zeros((2, nw, 2), dtype=np.int64)  # [parity][word] = (bits, epoch); epoch 0 = never written
+    e, r = epoch0, 0
+    while True:
+        e += 1
+        mine = count == 0
+        count[mine] = -1  # leaves for good (non_dominate.py:103)
+        words = np.zeros((nw, 2), dtype=np.int64)
+        own_words = np.unique(np.concatenate([np.arange(c * (CHUNK // 32), (c + 1) * (CHUNK // 32))
+                                              for c in range(first, first + nlocal * stride, stride)])) if nlocal else np.zeros(0, np.int64)
+        words[own_words, 1] = e  # every owned word is published every front, zero or not
+        np.add.at(words[:, 0], word_of[mine], np.left_shift(1, cols[mine] % 32).astype(np.int64))
+        gathered = all_gather(words)
+        slot = buffers[e & 1]
+        for q, w in enumerate(gathered):
+            sel = w[:, 1] == e
+            assert not np.any(sel & (slot[:, 1] == e)), "two ranks published the same word"
+            slot[sel] = w[sel]
+        assert np.all(slot[:, 1] == e), "a word of this front is missing: the reader would spin"
+        bits = slot[:, 0]
+        members = np.nonzero((bits[:, None] >> np.arange(32)) & 1)
+        members = members[0] * 32 + members[1]
+        members = members[members < n]
+        if len(members) == 0:
+            return ranks, r, e
+        ranks[members] = r
+        count -= np.where(count >= 0, d[members].sum(axis=0), 0)
+        r += 1
+
+
 class ShardedSelector:
     """Holds the NCCL communicator and workspace of one rank; all ranks must make the same calls."""
 

@@ -36,7 +36,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, n, m, seed, out):
+def _worker(rank, world, port, n, m, seed, out, flow=False):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch
@@ -61,9 +61,16 @@ def _worker(rank, world, port, n, m, seed, out):
         dist.all_gather(outs, t)
         return [o.numpy() for o in outs]
 
-    ranks, rounds = sharded.simulate_exchange(dominates_cols, n, rank, world, all_gather)
     want = nds_oracle.non_dominated_sort(x)
-    out[rank] = (bool(np.array_equal(ranks, want)), rounds, int(want.max()) + 1)
+    if flow:
+        # two calls in a row: the second continues from the first one's epoch (buffers are never cleared)
+        ranks, fronts, e1 = sharded.simulate_flow_exchange(dominates_cols, n, rank, world, all_gather)
+        ranks2, fronts2, e2 = sharded.simulate_flow_exchange(dominates_cols, n, rank, world, all_gather, epoch0=e1)
+        ok = bool(np.array_equal(ranks, want) and np.array_equal(ranks2, want) and fronts == fronts2 and e2 == 2 * e1)
+        out[rank] = (ok, fronts + 1, int(want.max()) + 1)
+    else:
+        ranks, rounds = sharded.simulate_exchange(dominates_cols, n, rank, world, all_gather)
+        out[rank] = (bool(np.array_equal(ranks, want)), rounds, int(want.max()) + 1)
     dist.destroy_process_group()
 
 
@@ -117,3 +124,19 @@ def test_flow_plan_tiles_every_column_once(n, nranks):
         assert int(words.max()) == max_words.value
         assert max_words.value * 128 <= 96 * 1024                              # counts of a CTA's columns in shared memory
     assert np.all(seen == 1)
+
+
+@pytest.mark.parametrize("n,m", [(9000, 3), (12300, 2)])
+def test_flow_exchange_protocol_two_gloo_ranks(n, m):
+    """The data-flow peel's exchange (tagged words, epoch parity, every rank stops on the same empty front)."""
+    import torch.multiprocessing as mp
+
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), n, m, 11, out, True), nprocs=world, join=True)
+    assert len(out) == world
+    for r in range(world):
+        ok, rounds, fronts = out[r]
+        assert ok, f"rank {r}: ranks differ from the oracle"
+        assert rounds == fronts + 1  # exactly one empty front is exchanged
