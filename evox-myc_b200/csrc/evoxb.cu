@@ -412,9 +412,10 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     if (fl.ok) {
         if (peel_mode_env() == 1) return run_peel_flow(L, n, rank, perm, fl, -1, s);
         if (peel_use_flow(n, m)) {
-            // front 0 is the smallest of the early fronts: n / 96 separates the measured cases (uniform M = 3..5 at
-            // 32768..131072 rows, NSGA-II on DTLZ2 from random to converged populations) by which kernel is faster
-            front0_limit = (int)(n / 96);
+            // front 0 is the smallest of the early fronts (uniform M = 3: a tenth of the average front; NSGA-II on
+            // DTLZ2: a third).  The data-flow kernel wins up to about 2000 rows per front, which n / 32 separates in the
+            // measured cases (uniform M = 3..4 at 32768..131072 rows, NSGA-II on DTLZ2 from random to converged)
+            front0_limit = (int)(n / 32);
             if (int rc = run_peel_flow(L, n, rank, perm, fl, front0_limit, s)) return rc;
         }
     }

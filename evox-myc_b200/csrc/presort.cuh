@@ -91,8 +91,27 @@ presort_coop_kernel(const float *__restrict__ x, int n, int m, int npad, Presort
             dst = (dst == perm_a) ? perm_b : perm_a;
         }
     };
-    run_passes(passes.fast_first, passes.count);
-    if (passes.fast_first > 0) {
+    // Which path: the fast one needs every value of key_0 to occur at most kPresortRunMax times.  Real populations
+    // break that (objectives clipped at a bound: hundreds of rows with f_0 == 0 in a converged NSGA-II run), and
+    // finding it out after four wasted passes costs more than asking first: a hashed multiplicity count of key_0
+    // (buckets in perm_b, which is free until the first pass) raises *slow_flag when any bucket exceeds the limit
+    // -- a bucket holds every copy of a value, so no flag means no long run (collisions only err to the slow side).
+    bool fast = passes.fast_first > 0;
+    if (fast) {
+        int nb = 4096;
+        while (nb * 2 <= npad && nb < 262144) nb *= 2;
+        for (int q = blockIdx.x * 256 + threadIdx.x; q < nb; q += gridDim.x * 256) perm_b[q] = 0u;
+        grid.sync();
+        for (int p = blockIdx.x * 256 + threadIdx.x; p < n; p += gridDim.x * 256) {
+            uint32_t k0 = float_to_key(x[(int64_t)p * m]);
+            k0 = (k0 ^ (k0 >> 15)) * 0x9E3779B1u;
+            if (atomicAdd(perm_b + (k0 >> 8) % (uint32_t)nb, 1u) >= (uint32_t)kPresortRunMax) atomicOr(slow_flag, 1);
+        }
+        grid.sync();
+        fast = *reinterpret_cast<volatile int *>(slow_flag) == 0;
+    }
+    run_passes(fast ? passes.fast_first : 0, passes.count);
+    if (fast) {
         uint32_t *cur = const_cast<uint32_t *>(src);
         for (int p = blockIdx.x * 256 + threadIdx.x; p < n; p += gridDim.x * 256) {
             const uint32_t k0 = float_to_key(x[(int64_t)__ldcg(cur + p) * m]);
