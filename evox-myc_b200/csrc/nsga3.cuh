@@ -311,8 +311,8 @@ n3_unit_refs_kernel(const float *__restrict__ ref, int r, int m, float *__restri
 }
 
 // ---- nsga3.py:134-142: perpendicular distance to every direction, nearest one (NaN skipped, first on ties) ----
-// Sixteen threads share four kept rows: thread s of the sixteen takes the directions j = s (mod 16) of every tile (a
-// direction read from shared memory serves the four rows), and the sixteen partial (distance, index) minima are merged
+// Eight threads share two kept rows: thread s of the eight takes the directions j = s (mod 8) of every tile (a
+// direction read from shared memory serves both rows), and the eight partial (distance, index) minima are merged
 // by shuffles, the smaller index winning among equal distances.  Directions are staged as float4-padded records
 // (a record is ceil(M / 4) 16-byte loads); the dot
 // product runs k = 0 .. M-1 in one FMA chain.
@@ -321,8 +321,8 @@ struct N3Tile {
     static constexpr int kPad = (M + 3) / 4 * 4;
     static constexpr int value = 8192 / kPad;  // directions per shared-memory tile (32 KB of floats)
 };
-constexpr int kN3Rows = 4;                            // rows per thread group
-constexpr int kN3Split = 16;                          // threads per group (slices of the directions)
+constexpr int kN3Rows = 2;                            // rows per thread group (4 rows x 16 slices measured slower: 95 registers)
+constexpr int kN3Split = 8;                           // threads per group (slices of the directions)
 constexpr int kN3RowsPerCta = 256 / kN3Split * kN3Rows;  // 64
 
 template <int M>
