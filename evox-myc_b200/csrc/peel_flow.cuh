@@ -36,13 +36,14 @@ constexpr int kFlowWarps = kFlowThreads / 32;
 constexpr int kUnitWords = 8;                                // 256 columns
 constexpr int kUnitsPerChunk = kChunkWords / kUnitWords;     // 16
 constexpr int kFlowMaxPieces = 32;                           // per CTA
-constexpr int kFlowStageCap = 8192;                          // members staged per round
+constexpr int kFlowStageCap = 16384;                         // members staged per round
 constexpr int kFlowMaxChunks = 128;                          // N <= 524288 (front words are kept in shared memory)
 constexpr int kFlowMaxCountPlanes = 20;
 constexpr int kFlowMaxRanks = 16;
 constexpr int kFlowMaxCtas = 192;                            // flag slots per rank (one CTA per SM)
 constexpr int kFlowTileWords = 8192;                         // shared-memory tile of the small path / gather scratch of the large one
-constexpr int kFlowAuxWords = 12 * kFlowThreads;               // per-thread row planes parked for the merge
+constexpr int kFlowStreamPlanes = 9;                         // streaming mode: a stream adds at most 2^9 - 8 rows
+constexpr int kFlowAuxWords = kFlowStreamPlanes * 4 * kFlowThreads;  // per-thread row planes parked for the merge
 
 #ifndef EVOXB_FLOW_TIMING
 #define EVOXB_FLOW_TIMING 0
@@ -287,7 +288,7 @@ struct FlowShared {
 //    the next front, published on the spot (tagged, to every rank).
 // Latency matters here, not work: a front is a few dozen rows per CTA, so every serial chain was kept short.
 constexpr int kFlowRowPlanes = 12;   // a thread adds at most 8192 / 4 rows
-constexpr int kFlowGroupPlanes = 7;  // at most 64 groups
+constexpr int kFlowGroupPlanes = 9;  // at most 256 groups / streams
 
 // nm == 0: nothing to subtract, only detect and publish.  `publish` is false while more rounds of the same
 // front are still to be subtracted (fronts above kFlowStageCap members).
@@ -315,6 +316,56 @@ __device__ __forceinline__ void flow_piece_pass(const FlowArgs &a, const FlowPie
         uint4 *tile4 = reinterpret_cast<uint4 *>(sm.tile);
         const int w = t & (W - 1), g = t >> lg_w;
 
+        // Two ways to add the rows.  A front of more than one tile is bandwidth work: every thread then streams
+        // rows straight from global memory, eight 16-byte loads in flight, into its own bit planes (no tile, no
+        // barrier per tile) and the 512 / parts streams are merged like the groups below.  Smaller fronts go
+        // through the shared-memory tile, where threads are (word, group) and the merge is short.
+        const int nstreams = kFlowThreads >> lg_parts;
+        const bool streaming = nm > rows_per_tile && nm <= ((1 << kFlowStreamPlanes) - 2 * kBatch) * nstreams;
+        if (streaming) {
+            const int strm = t >> lg_parts;
+            ng = nstreams;
+            lg_ng = kFlowLgThreads - lg_parts;
+            uint32_t p4[4][kFlowStreamPlanes];
+#pragma unroll
+            for (int s4 = 0; s4 < 4; ++s4)
+#pragma unroll
+                for (int p = 0; p < kFlowStreamPlanes; ++p) p4[s4][p] = 0u;
+#pragma unroll 1
+            for (int q0 = strm * kBatch; q0 < nm; q0 += nstreams * kBatch) {
+                uint4 vv[kBatch];
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) {
+                    const int q = q0 + b;
+                    const int row = sm.rows[min(q, nm - 1)];
+                    const bool fetch = q < nm && (!tri || (row >> 12) <= pc.chunk) && !(sm.tmin[row >> 10] > col_max);
+                    vv[b] = ldg_stream_v4_if(base + a.rows.vstart(row), fetch);
+                }
+                uint32_t in[kBatch];
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) in[b] = vv[b].x;
+                flow_add8<kFlowStreamPlanes>(p4[0], in);
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) in[b] = vv[b].y;
+                flow_add8<kFlowStreamPlanes>(p4[1], in);
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) in[b] = vv[b].z;
+                flow_add8<kFlowStreamPlanes>(p4[2], in);
+#pragma unroll
+                for (int b = 0; b < kBatch; ++b) in[b] = vv[b].w;
+                flow_add8<kFlowStreamPlanes>(p4[3], in);
+            }
+            // a stream takes whole batches of kBatch rows: at most kBatch * ceil(nm / (kBatch * streams)) of them
+            np = 32 - __clz(kBatch * ((nm + kBatch * ng - 1) / (kBatch * ng)));
+#pragma unroll
+            for (int p = 0; p < kFlowStreamPlanes; ++p)
+                if (p < np) {
+#pragma unroll
+                    for (int s4 = 0; s4 < 4; ++s4) sm.aux[(((p << lg_ng) + strm) << lg_w) + part * 4 + s4] = p4[s4][p];
+                }
+            __syncthreads();
+            FLOW_T(5)
+        } else {
         uint32_t pl[kFlowRowPlanes];
 #pragma unroll
         for (int p = 0; p < kFlowRowPlanes; ++p) pl[p] = 0u;
@@ -369,6 +420,7 @@ __device__ __forceinline__ void flow_piece_pass(const FlowArgs &a, const FlowPie
                 if (p < np) sm.aux[(((p << lg_ng) + g) << lg_w) + w] = pl[p];  // [plane][group][word]
         }
         __syncthreads();
+        }
         FLOW_T(6)
         if (ng > 8) {  // thread (word, plane): count of that plane's bits over the groups, kg planes, parked in the tile
             merged = true;
