@@ -321,7 +321,7 @@ struct N3Tile {
     static constexpr int kPad = (M + 3) / 4 * 4;
     static constexpr int value = 8192 / kPad;  // directions per shared-memory tile (32 KB of floats)
 };
-constexpr int kN3Rows = 2;                            // rows per thread group (4 rows x 16 slices measured slower: 95 registers)
+constexpr int kN3Rows = 2;                            // rows per thread group (4 measured slower: 95 registers)
 constexpr int kN3Split = 8;                           // threads per group (slices of the directions)
 constexpr int kN3RowsPerCta = 256 / kN3Split * kN3Rows;  // 64
 
@@ -339,7 +339,7 @@ n3_associate_kernel(const float *__restrict__ xu, const float *__restrict__ xnor
     float nn[kN3Rows], x[kN3Rows][kPad], best[kN3Rows];
     int arg[kN3Rows];
     bool some[kN3Rows], ok[kN3Rows];
-    float sthr[kN3Rows];
+    float sthr[kN3Rows], smax[kN3Rows];
 #pragma unroll
     for (int q = 0; q < kN3Rows; ++q) {
         const int slot = blockIdx.x * kN3RowsPerCta + group * kN3Rows + q;
@@ -352,6 +352,7 @@ n3_associate_kernel(const float *__restrict__ xu, const float *__restrict__ xnor
         some[q] = false;
         ok[q] = nn[q] > 0.0f && nn[q] < __int_as_float(0x7f800000);
         sthr[q] = __int_as_float(0x7f800000);
+        smax[q] = __int_as_float(0xff800000);
     }
     for (int j0 = 0; j0 < r; j0 += kTile) {
         const int jn = min(kTile, r - j0);
@@ -379,7 +380,9 @@ n3_associate_kernel(const float *__restrict__ xu, const float *__restrict__ xnor
                 // still be <= the best one (two roundings of <= 2^-24 each separate d from |x| sqrt(s))
                 const float sq = __fsub_rn(1.0f, __fmul_rn(c, c));
                 if (ok[q]) {
-                    some[q] = some[q] || (sq >= 0.0f);
+                    // `seen` (a distance that is not NaN exists) only matters for rows that end without a direction;
+                    // it is recovered after the loop from the largest sq (fmaxf skips NaN)
+                    smax[q] = fmaxf(smax[q], sq);
                     if (sq <= sthr[q]) {
                         const float d = nn[q] * sqrtf(sq);
                         if (d < best[q]) {  // NaN compares false: skipped; strict: the first of equal distances stays
@@ -401,6 +404,7 @@ n3_associate_kernel(const float *__restrict__ xu, const float *__restrict__ xnor
     }
 #pragma unroll
     for (int q = 0; q < kN3Rows; ++q) {
+        if (ok[q]) some[q] = smax[q] >= 0.0f;  // finite |x| > 0: d is a number exactly when 1 - cos^2 >= 0
         // merge the slices: smaller distance, then smaller direction index (NaN never entered `best`)
 #pragma unroll
         for (int o = 1; o < kN3Split; o <<= 1) {
