@@ -73,7 +73,9 @@ def ncu_traffic_per_launch(kernel_substr: str, n: int, m: int, world: int = 1):
     import csv
     import glob
 
-    tag = f"N{n}_M{m}" + (f"_w{world}" if world > 1 else "")
+    # multi-GPU: the per-rank kernel is captured on a one-rank communicator (never ncu a multi-rank command);
+    # a rank of `world` streams 1 / world of those bytes
+    tag = f"N{n}_M{m}" + ("_w1" if world > 1 else "")
     best = None
     for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", f"launches_*_{tag}_v*.csv"))):
         best = path  # the latest version of the latest round
@@ -102,7 +104,10 @@ def ncu_traffic_per_launch(kernel_substr: str, n: int, m: int, world: int = 1):
         return None, f"{rel}: unreadable ({ex!r})"
     if not (launches and tot):
         return None, f"{rel} holds no launch of {kernel_substr}"
-    return tot / launches, f"ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, {rel} (sources {want})"
+    note = f"ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, {rel} (sources {want})"
+    if world > 1:
+        return tot / launches / world, note + f", one-rank capture divided by {world} ranks"
+    return tot / launches, note
 
 
 def measured_peaks():
@@ -377,7 +382,14 @@ def run_gpu_arm(args, n, m, desc):
         peel_kernel = {"data-flow peer-memory kernel": "peel_flow_kernel (tagged words stored to the peers over NVLink)",
                        "grid-wide peer-memory kernel": "peel_p2p_kernel (tagged words stored to the peers over NVLink)",
                        }.get(exchange["path"], "front_subtract_kernel (+ detect / ncclAllGather / expand per front)")
-    ncu_bytes, ncu_src = ncu_traffic_per_launch("peel_persistent_kernel" if world == 1 else "peel_p2p_kernel", n, m, world)
+    if world == 1:
+        # both peel kernels may have been enqueued; the one that returned at once moved (almost) no bytes
+        cands = [ncu_traffic_per_launch(k, n, m, 1) for k in (("peel_flow_kernel", "peel_persistent_kernel") if flow_possible
+                                                                else ("peel_persistent_kernel",))]
+        ncu_bytes, ncu_src = max(cands, key=lambda c: c[0] or 0.0)
+    else:
+        ncu_bytes, ncu_src = ncu_traffic_per_launch("peel_flow_kernel" if exchange["path"].startswith("data-flow") else "peel_p2p_kernel",
+                                                    n, m, world)
     if peel_ms:
         ach = alg_bytes / (peel_ms * 1e-3) / 1e9
         roofline = {"kernel": peel_kernel,

@@ -12,7 +12,8 @@ KEYS = ['Block Size', 'Grid Size', 'gpu__time_duration.sum', 'dram__bytes_read.s
         'stalled_long_scoreboard_per_issue', 'stalled_math_pipe_throttle_per_issue', 'stalled_no_instruction_per_issue', 'stalled_short_scoreboard_per_issue',
         'stalled_wait_per_issue', 'dram__cycles_active.avg.pct', 'launch__shared_mem_per_block', 'sm__warps_active.avg.per_cycle_active',
         'lts__t_bytes.sum', 'lts__throughput.avg.pct']
-for rep, out in [("prof_c4.ncu-rep", f"ncu_full_c4_N262144_M5_summary_{suf}.csv"), ("prof_c2.ncu-rep", f"ncu_full_c2_N65536_M3_summary_{suf}.csv")]:
+for rep, out in [("prof_c4.ncu-rep", f"ncu_full_c4_N262144_M5_summary_{suf}.csv"), ("prof_c2.ncu-rep", f"ncu_full_c2_N65536_M3_summary_{suf}.csv"),
+                 ("prof_c5n3.ncu-rep", f"ncu_full_c5_nsga3_N65536_M10_summary_{suf}.csv")]:
     path = os.path.join(src, rep)
     if not os.path.exists(path):
         continue
@@ -27,8 +28,8 @@ for rep, out in [("prof_c4.ncu-rep", f"ncu_full_c4_N262144_M5_summary_{suf}.csv"
         for h in keep:
             w.writerow([h, units[idx[h]]] + [r[idx[h]] for r in rows[2:]])
     print("wrote", out)
-for path in sorted(glob.glob(os.path.join(src, "launches_*_v1.csv"))):
-    base = os.path.basename(path).replace("_v1.csv", f"_{suf}.csv")
+for path in sorted(glob.glob(os.path.join(src, f"launches_*_{suf}.csv"))):
+    base = os.path.basename(path)
     shutil.copy(path, os.path.join(rdir, base))
     shutil.copy(path + ".meta.json", os.path.join(rdir, base + ".meta.json"))
     lr = list(csv.reader(l for l in open(path) if l.startswith('"')))
