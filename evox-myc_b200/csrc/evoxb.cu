@@ -223,8 +223,8 @@ constexpr size_t kFlowSmemLimit = 200 * 1024;
 
 // Picks two CTAs per SM when they fit, else one; the plan (column ownership) depends on that choice.
 // Cached per (thread, device, shape): the plan walks every piece on the host.
-static int flow_prepare(int nchunks, ChunkMap cm, bool tri, int count_planes, FlowLaunch *out) {
-    struct Entry { int dev, nchunks, first, stride, nlocal, tri, cp; FlowLaunch fl; };
+static int flow_prepare(int nchunks, ChunkMap cm, bool tri, FlowLaunch *out) {
+    struct Entry { int dev, nchunks, first, stride, nlocal, tri; FlowLaunch fl; };
     static thread_local Entry cache[8];
     static thread_local int used = 0, next = 0;
     int dev = 0;
@@ -232,14 +232,14 @@ static int flow_prepare(int nchunks, ChunkMap cm, bool tri, int count_planes, Fl
     for (int i = 0; i < used; ++i) {
         const Entry &e = cache[i];
         if (e.dev == dev && e.nchunks == nchunks && e.first == cm.first && e.stride == cm.stride && e.nlocal == cm.nlocal &&
-            e.tri == (int)tri && e.cp == count_planes) {
+            e.tri == (int)tri) {
             *out = e.fl;
             return 0;
         }
     }
     FlowLaunch fl{};
     fl.ok = false;
-    if (nchunks <= kFlowMaxChunks && cm.nlocal >= 1 && count_planes <= kFlowMaxCountPlanes) {
+    if (nchunks <= kFlowMaxChunks && cm.nlocal >= 1) {
         static std::mutex mu;
         static bool attr_set[64] = {};
         if (dev >= 0 && dev < 64) {
@@ -254,7 +254,7 @@ static int flow_prepare(int nchunks, ChunkMap cm, bool tri, int count_planes, Fl
         for (int per_sm = 1; per_sm >= 1 && !fl.ok; --per_sm) {
             FlowPlan plan = flow_make_plan(nchunks, cm, tri, sms * per_sm);
             if (plan.grid < 1 || plan.max_pieces > kFlowMaxPieces) continue;
-            const size_t smem = flow_smem_bytes(nchunks, count_planes, plan.max_words);
+            const size_t smem = flow_smem_bytes(nchunks, plan.max_words);
             if (smem > kFlowSmemLimit) continue;
             int occ = 0;
             EVOXB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, peel_flow_kernel, kFlowThreads, smem));
@@ -264,7 +264,7 @@ static int flow_prepare(int nchunks, ChunkMap cm, bool tri, int count_planes, Fl
             fl.ok = true;
         }
     }
-    Entry ne{dev, nchunks, cm.first, cm.stride, cm.nlocal, (int)tri, count_planes, fl};
+    Entry ne{dev, nchunks, cm.first, cm.stride, cm.nlocal, (int)tri, fl};
     if (used < 8) cache[used++] = ne;
     else { cache[next] = ne; next = (next + 1) % 8; }
     *out = fl;
@@ -301,7 +301,6 @@ static int run_peel_flow(const NdsLayout &L, int64_t n, int32_t *rank, const int
     a.nranks = 1;
     a.grids[0] = fl.plan.grid;
     a.slot_words = L.npad / 32;
-    a.count_planes = bits_for(n > 1 ? n : 2);
     a.max_words = fl.plan.max_words;
     a.target = fl.plan.target;
     a.fronts_done = &L.ctrl->fronts_done;
@@ -406,7 +405,7 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
     // enqueued and the size of front 0 decides on the device which one returns at once (no host round trip).
     FlowLaunch fl{};
     if (peel_mode_env() != 2) {
-        if (int rc = flow_prepare(L.nchunks, ChunkMap{0, 1, L.nchunks}, L.tri, bits_for(n > 1 ? n : 2), &fl)) return rc;
+        if (int rc = flow_prepare(L.nchunks, ChunkMap{0, 1, L.nchunks}, L.tri, &fl)) return rc;
     }
     int front0_limit = -1;  // -1: only the grid-wide kernel runs
     if (fl.ok) {
@@ -537,7 +536,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
         for (int q = 0; q < L.nranks && all_ok; ++q) {
             const ChunkMap cq{q, L.nranks, q < L.nchunks ? (L.nchunks - q + L.nranks - 1) / L.nranks : 0};
             FlowLaunch fq{};
-            if (int rc = flow_prepare(L.nchunks, cq, true, bits_for(n > 1 ? n : 2), &fq)) return rc;
+            if (int rc = flow_prepare(L.nchunks, cq, true, &fq)) return rc;
             all_ok = all_ok && fq.ok;
             a.grids[q] = fq.plan.grid;
             if (q == comm->rank) mine = fq;
@@ -556,8 +555,7 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
             a.me = comm->rank;
             a.nranks = L.nranks;
             a.slot_words = (int64_t)kFlowMaxChunks * kChunkWords;
-            a.count_planes = bits_for(n > 1 ? n : 2);
-            a.max_words = mine.plan.max_words;
+                    a.max_words = mine.plan.max_words;
             a.target = mine.plan.target;
             a.fronts_done = comm->fronts_dev;
             a.host_error = comm->h_err;

@@ -5,25 +5,25 @@
 // spreads every front evenly over the grid and pays two grid-wide syncs, a prefix and an atomic flush
 // per front (about 16 us); for populations whose fronts are small that fixed cost IS the peel time.
 // Here every CTA OWNS a fixed set of matrix columns:
-//   * the dominator counts of its columns live in its shared memory as bit planes (plane p holds
-//     bit p of 32 counts per word), so "subtract the column sums of this front's rows" is a
-//     bit-sliced subtraction and "which counts reached zero" is an OR over the planes -- no global
-//     atomics, no integer expansion, and the result IS the next front's bitmask word;
+//   * the dominator counts of its columns live in its shared memory (one int per column, -1 once the column has
+//     left), so subtracting a front needs no global atomics, and the warp ballot of "count reached zero" IS the
+//     column word of the next front;
 //   * a front travels between CTAs as tagged words: every 32-column word of the front bitmask is one
-//     8-byte {word, epoch} store (arrives whole), readers spin on the tag of the word they need.  No
-//     fence, no flag, no barrier.  Every CTA reads the complete bitmask of a front before it publishes
-//     its share of the next one, which bounds run-ahead to one front and makes two buffers (epoch
-//     parity) enough; every CTA sees the same bitmask, so all of them stop at the same (empty) front;
-//   * the same tagged stores go to the peer GPUs' buffers over NVLink in the multi-GPU build of the
-//     loop (peers[] holds one buffer per rank; a single GPU has one entry in its own workspace).
-// Critical path per front: publish -> L2 -> poll -> compaction -> one batch of row loads -> bit-sliced
-// reduction -> subtract/detect, i.e. a few thousand clocks instead of 16 us.
+//     8-byte {word, epoch} store (arrives whole) into a double buffer, and a word is valid when its tag is the
+//     epoch being read.  No fence and no barrier.  Every CTA reads the complete bitmask of a front before it
+//     publishes its share of the next one, which bounds run-ahead to one front and makes two buffers (epoch
+//     parity) enough; every CTA sees the same bitmask, so all of them stop at the same (empty) front.  A progress
+//     flag per CTA (polled by one warp) only tells WHEN reading the words is worthwhile;
+//   * the same tagged stores and flags go to the peer GPUs' buffers over NVLink in the multi-GPU use of the
+//     kernel (peers[] holds one buffer per rank; a single GPU has one entry in its own workspace).
+// Per front and CTA: flags -> the front's words -> staged member rows -> the piece's bytes of those rows (through
+// a shared-memory tile, or streamed straight into per-thread bit planes when the front is large) -> Harley-Seal
+// adds -> one thread per column subtracts and detects -> tagged stores of the next front.
 //
 // Column ownership: a matrix row is cut in units of 256 columns (32 bytes).  A chunk (4096 columns)
 // is split in 1..16 pieces of equal width, narrower where more rows have bits (chunk c of the
 // presorted, triangular matrix only takes rows of chunks <= c, weight c + 1); pieces are dealt to the
-// CTAs round-robin in order of decreasing chunk.  Threads of a CTA form `256 / parts` streams over the
-// members (part = 16 bytes of the piece), every stream keeps 8 row loads in flight.
+// CTAs round-robin in order of decreasing chunk, one piece per CTA whenever there are enough columns.
 #pragma once
 
 #include "peel.cuh"
@@ -38,7 +38,6 @@ constexpr int kUnitsPerChunk = kChunkWords / kUnitWords;     // 16
 constexpr int kFlowMaxPieces = 32;                           // per CTA
 constexpr int kFlowStageCap = 16384;                         // members staged per round
 constexpr int kFlowMaxChunks = 128;                          // N <= 524288 (front words are kept in shared memory)
-constexpr int kFlowMaxCountPlanes = 20;
 constexpr int kFlowMaxRanks = 16;
 constexpr int kFlowMaxCtas = 192;                            // flag slots per rank (one CTA per SM)
 constexpr int kFlowTileWords = 8192;                         // shared-memory tile of the small path / gather scratch of the large one
@@ -149,7 +148,6 @@ struct FlowArgs {
     int me, nranks;
     int grids[kFlowMaxRanks];  // CTAs of every rank's kernel (they all publish, so they all are waited for)
     int64_t slot_words;   // words per parity buffer (>= npad / 32)
-    int count_planes;     // bits needed for a dominator count (<= kFlowMaxCountPlanes)
     int max_words;        // FlowPlan::max_words (shared-memory layout)
     long long target;     // FlowPlan::target
     int *fronts_done;     // out (device): number of fronts, -1 after a time-out
@@ -196,11 +194,10 @@ struct FlowSmemLayout {
     float *tmax;       // [ntiles] largest (copy of TileBands::tmax; +inf without band information)
 };
 
-__host__ __device__ inline size_t flow_smem_bytes(int nchunks, int count_planes, int max_words) {
+__host__ __device__ inline size_t flow_smem_bytes(int nchunks, int max_words) {
     size_t b = (size_t)kFlowStageCap * 4;               // rows
     b += (size_t)kFlowTileWords * 4;                    // tile
     b += (size_t)kFlowAuxWords * 4;                     // aux
-    (void)count_planes;
     b += (size_t)max_words * 32 * 4;                    // counts
     b += (size_t)nchunks * 4 * 4 * 2;                   // tmin, tmax
     return b;

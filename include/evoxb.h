@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define EVOXB_VERSION 100 /* 0.1.0 */
+#define EVOXB_VERSION 200 /* 0.2.0 */
 
 #if defined(__GNUC__)
 #define EVOXB_API __attribute__((visibility("default")))
