@@ -66,6 +66,17 @@ def library_source_hash() -> str:
     return h.hexdigest()[:16]
 
 
+def build_uses_levels(n, m):
+    """Whether the library builds the dominance matrix of this shape from 15-bit levels (csrc/levels.cuh)."""
+    import ctypes
+
+    from evox_myc_b200 import _lib
+
+    path = ctypes.c_int(0)
+    _lib.check(_lib.lib().evoxb_nds_build_path(None, n, m, None, ctypes.byref(path)))
+    return path.value == 1
+
+
 def ncu_traffic_per_launch(kernel_substr: str, n: int, m: int, world: int = 1):
     """DRAM bytes (read + write) per launch of a kernel from the committed ncu launch list of the same
     workload (profiles/).  The capture's side file (<csv>.meta.json, written by the capture script) holds
@@ -413,8 +424,11 @@ def run_gpu_arm(args, n, m, desc):
         peak_ops = 148 * 64 * clk * 1e6
         pairs_rank = float(n) * n / world
         ach_ops = 2.0 * m * pairs_rank / (build_ms * 1e-3)
-        extra.append({"kernel": "dominance_build_tri_kernel" if tri else "dominance_build_kernel",
-                      "bound": "alu (fp32 compare pipe, 64 lanes/clk/SM)",
+        levels = build_uses_levels(n, m)
+        extra.append({"kernel": ("dominance_build_lvl_kernel (15-bit levels; the stage also holds the level_* set-up and fix-up kernels)"
+                                 if levels else "dominance_build_tri_kernel" if tri else "dominance_build_kernel"),
+                      "bound": ("integer pipes: ALU (LOP3 + VOTE) and FMA (IMAD), 64 lanes/clk/SM each; peak below = the float "
+                                "kernel's compare pipe" if levels else "alu (fp32 compare pipe, 64 lanes/clk/SM)"),
                       "achieved": ach_ops / 1e12, "peak": peak_ops / 1e12, "unit": "Tcompare/s", "frac": ach_ops / peak_ops,
                       "executed": None, "executed_frac": None,
                       "ms_per_launch": build_ms, "pairs_per_s": pairs_rank / (build_ms * 1e-3)})

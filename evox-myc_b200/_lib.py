@@ -44,6 +44,7 @@ EXPORTS = [
     "evoxb_comm_poll_error",
     "evoxb_comm_set_timeout_ms",
     "evoxb_comm_last_path",
+    "evoxb_nds_build_path",
     "evoxb_shard_plan",
     "evoxb_flow_plan",
     "evoxb_nds_sharded_workspace_bytes",
@@ -102,6 +103,7 @@ def lib() -> ctypes.CDLL:
         L.evoxb_comm_poll_error.argtypes = [vp]
         L.evoxb_comm_set_timeout_ms.argtypes = [vp, i64]
         L.evoxb_comm_last_path.argtypes = [vp]
+        L.evoxb_nds_build_path.argtypes = [vp, i64, i32, vp, ip]
         L.evoxb_shard_plan.argtypes = [i64, i32, i32, ip, ip, ip, ip]
         L.evoxb_flow_plan.argtypes = [i64, i32, i32, i32, i32, ip, ip, ip, ctypes.POINTER(ctypes.c_int32), i32]
         L.evoxb_nds_sharded_workspace_bytes.argtypes = [i64, i32, i32, i32, ctypes.POINTER(sz)]

@@ -176,8 +176,8 @@ inline int launch_dominance_build(const float *xt, int64_t npad, int64_t row0, i
 // Rows are in lexicographic order (presort.cuh), so D[i][j] = (uid_i < uid_j) & all_{k>=1}(x_ik <= x_jk):
 // M-1 float compares + 1 integer compare per pair instead of 2 M, and only tiles that reach above
 // the diagonal are computed.  Row tiles (128 rows) are grouped in bands of 32 (= one 4096-column
-// chunk); band b needs column tiles 4 b .. ntc-1.  Tiles of the diagonal chunk that lie entirely
-// left of their rows are written as zeros because the peel streams whole 512-byte chunks.
+// chunk); band b needs column tiles 4 b .. ntc-1 (inside the diagonal chunk positions carry no order, so
+// all of its tiles are computed).
 struct TriGrid {
     int ntc;     // column tiles (npad / 1024)
     int nrt;     // row tiles of this launch
@@ -203,31 +203,18 @@ inline TriGrid make_tri_grid(int64_t npad, int64_t n_rows) {
     return g;
 }
 
-// kPacked: triangular storage (TriRows::vstart); the rectangular instance keeps the plain row * stride addressing
-template <int M, bool kPacked>
-__global__ void __launch_bounds__(kBuildThreads)
-dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows, const int *__restrict__ uid_row,
-                           const int *__restrict__ uid_col, const float *__restrict__ tile_min1,
-                           const float *__restrict__ tile_max1, uint32_t *__restrict__ D, TriRows rows, TriGrid g) {
-    constexpr int K = (M > 1) ? (M - 1) : 1;  // objectives 1..M-1 are compared
-    __shared__ float xs[kTileRows][K];
-    __shared__ int us[kTileRows];
-    __shared__ __align__(16) uint32_t stage[kBuildThreads / 32][32][kC];  // per warp: 32 rows x 4 ballot words
-    __shared__ float rb_min1[kTileRows / 32], rb_max1[kTileRows / 32];     // band of objective 1 per 32-row block
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-
-    int rt, ct;
-    int64_t word0;  // word offset of the tile's first column inside a (local) matrix row
+// Tile id -> (row tile, column tile, word offset of the tile's first column inside a (local) matrix row).
+// (bx, by) are the block indices of the one-tile-per-CTA launch: bx = tile id (one GPU) or local column tile
+// (sharded), by = row tile (sharded).  Returns false for a sharded tile left of its rows' chunk (never read).
+__device__ __forceinline__ bool tri_tile_coords(const TriGrid &g, long long bx, int by, int &rt, int &ct, int64_t &word0) {
     if (g.sharded) {
-        const int lct = blockIdx.x, lc = lct >> 2, c = g.cm.global(lc);
-        rt = blockIdx.y;
-        if (c < (rt >> 5)) return;  // chunk entirely left of the rows' own chunk: never read by the peel
+        const int lct = (int)bx, lc = lct >> 2, c = g.cm.global(lc);
+        rt = by;
+        if (c < (rt >> 5)) return false;
         ct = c * 4 + (lct & 3);
         word0 = (int64_t)lct * (kTileCols / 32);
     } else {
-        // tile id -> (band, row tile, column tile)
-        const long long t = blockIdx.x;
+        const long long t = bx;
         int lo = 0, hi = g.nbands;  // before(lo) <= t < before(hi)
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
@@ -240,137 +227,34 @@ dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n
         ct = 4 * band + (int)(local % width);
         word0 = (int64_t)ct * (kTileCols / 32);
     }
+    return true;
+}
 
-    const int64_t tile_row0 = (int64_t)rt * kTileRows;
-    const int64_t tile_col0 = (int64_t)ct * kTileCols;
-    const int64_t col_base = tile_col0 + warp * (kC * 32);
-    const int64_t word_base = word0 + warp * kC;
-    // Tile-level test on objective 1 (rows inside a chunk are ordered by it, so a 1024-tile is a band of
-    // x_1; presort.cuh): if every row's x_1 exceeds every column's, nothing in the tile can dominate.
-    // (A column tile of the rows' own chunk may lie "left" of the rows: inside a chunk positions carry no
-    // order, so such tiles are computed like any other.)
-    bool sure1 = false;  // every row's x_1 <= every column's x_1: that compare is dropped for the tile
-    if (M > 1) {
-        const int rt1024 = (int)(tile_row0 / kTileCols);
-        const float r_lo = tile_min1[rt1024], r_hi = tile_max1[rt1024];
-        const float c_lo = tile_min1[ct], c_hi = tile_max1[ct];
-        if (r_lo > c_hi) {
-            for (int rb = 0; rb < kTileRows; rb += 32) {
-                const int64_t r = tile_row0 + rb + lane;
-                if (r < n_rows) *reinterpret_cast<uint4 *>((kPacked ? D + rows.vstart(r) * 4 + word_base : D + r * rows.row_words + word_base)) = make_uint4(0u, 0u, 0u, 0u);
-            }
-            return;
-        }
-        sure1 = r_hi <= c_lo;
-    }
+// One 128 x 1024 tile of the presorted matrix (body: dominance_tri_body.cuh).  kPacked: triangular storage
+// (TriRows::vstart); the rectangular instance keeps the plain row * stride addressing.
+template <int M, bool kPacked>
+__global__ void __launch_bounds__(kBuildThreads)
+dominance_build_tri_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows, const int *__restrict__ uid_row,
+                           const int *__restrict__ uid_col, const float *__restrict__ tile_min1,
+                           const float *__restrict__ tile_max1, uint32_t *__restrict__ D, TriRows rows, TriGrid g) {
+#define EVOXB_BX blockIdx.x
+#define EVOXB_BY blockIdx.y
+#include "dominance_tri_body.cuh"
+#undef EVOXB_BX
+#undef EVOXB_BY
+}
 
-    for (int q = threadIdx.x; q < kTileRows * K; q += kBuildThreads) {
-        const int r = q / K, k = q - r * K;
-        xs[r][k] = (M > 1 && tile_row0 + r < n_rows) ? xt[(int64_t)(k + 1) * npad + tile_row0 + r]
-                                                      : __int_as_float(0x7fc00000);
-    }
-    for (int r = threadIdx.x; r < kTileRows; r += kBuildThreads)
-        us[r] = (tile_row0 + r < n_rows) ? uid_row[tile_row0 + r] : 0x7fffffff;
-    float xj[kC][K];
-    int uj[kC];
-#pragma unroll
-    for (int c = 0; c < kC; ++c) {
-        uj[c] = uid_col[col_base + c * 32 + lane];
-#pragma unroll
-        for (int k = 0; k < K; ++k)
-            xj[c][k] = (M > 1) ? xt[(int64_t)(k + 1) * npad + col_base + c * 32 + lane] : 0.0f;
-    }
-    __syncthreads();
-
-    // If every row uid of the tile is below every column uid of this warp, the uid test is true for
-    // all of the warp's pairs and is dropped from the inner loop (the common case away from the
-    // diagonal; NaN rows / columns carry INT_MAX / 0 and force the full predicate).
-    int row_umax = max(max(us[lane], us[lane + 32]), max(us[lane + 64], us[lane + 96]));
-    int col_umin = min(min(uj[0], uj[1]), min(uj[2], uj[3]));
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        row_umax = max(row_umax, __shfl_xor_sync(0xffffffffu, row_umax, o));
-        col_umin = min(col_umin, __shfl_xor_sync(0xffffffffu, col_umin, o));
-    }
-    const bool need_uid = !(row_umax < col_umin);
-    uint32_t(*st)[kC] = stage[warp];
-
-    // Bands of objective 2 (rows inside a 1024-tile are ordered by it, presort.cuh): smallest / largest
-    // value of every 32-row block and of this warp's 128 columns.  fminf / fmaxf skip NaN; rows and
-    // columns holding a NaN are rejected by the uid test, which is always active when one is present.
-    constexpr int kB = (K > 1) ? 1 : 0;  // index of objective 2 in xs / xj
-    float c_min1 = 0.0f, c_max1 = 0.0f;
-    if (K > 1) {
-        c_min1 = fminf(fminf(xj[0][kB], xj[1][kB]), fminf(xj[2][kB], xj[3][kB]));
-        c_max1 = fmaxf(fmaxf(xj[0][kB], xj[1][kB]), fmaxf(xj[2][kB], xj[3][kB]));
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            c_min1 = fminf(c_min1, __shfl_xor_sync(0xffffffffu, c_min1, o));
-            c_max1 = fmaxf(c_max1, __shfl_xor_sync(0xffffffffu, c_max1, o));
-        }
-        if (warp < kTileRows / 32) {
-            float lo = xs[warp * 32 + lane][kB], hi = lo;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-                hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-            }
-            if (lane == 0) {
-                rb_min1[warp] = lo;
-                rb_max1[warp] = hi;
-            }
-        }
-        __syncthreads();
-    }
-
-    // One 32-row block against this warp's 128 columns.  WITH_UID: keep the uid compare.  DROP: bit k set =
-    // the compare of objective k+1 is known to hold for every pair of the block and is dropped.
-#define EVOXB_TRI_BLOCK(WITH_UID, DROP)                                                                    \
-    {                                                                                                       \
-        _Pragma("unroll 8") for (int ii = 0; ii < 32; ++ii) {                                               \
-            float xi[K];                                                                                    \
-            _Pragma("unroll") for (int k = 0; k < K; ++k) xi[k] = xs[rb + ii][k];                           \
-            const int ui = WITH_UID ? us[rb + ii] : 0;                                                      \
-            uint32_t b[kC];                                                                                 \
-            _Pragma("unroll") for (int c = 0; c < kC; ++c) {                                                \
-                bool p = WITH_UID ? (ui < uj[c]) : true;                                                    \
-                if (M > 1) {                                                                                \
-                    _Pragma("unroll") for (int k = 0; k < K; ++k)                                           \
-                        if (!((DROP) >> k & 1)) p = p && (xi[k] <= xj[c][k]);                               \
-                }                                                                                           \
-                b[c] = __ballot_sync(0xffffffffu, p);                                                       \
-            }                                                                                               \
-            /* the four words of row ii are warp-uniform: one lane parks them in shared memory */          \
-            if (lane == 0) *reinterpret_cast<uint4 *>(st[ii]) = make_uint4(b[0], b[1], b[2], b[3]);         \
-        }                                                                                                   \
-        __syncwarp();                                                                                       \
-        v = *reinterpret_cast<const uint4 *>(st[lane]);                                                     \
-        __syncwarp();                                                                                       \
-    }
-
-    for (int rb = 0; rb < kTileRows; rb += 32) {
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        // no row of the block can satisfy x_i2 <= x_j2 for any column of the warp: the words stay zero
-        const bool dead = (K > 1) && (rb_min1[rb >> 5] > c_max1);
-        // every row of the block satisfies it for every column: the compare is dropped
-        const bool sure2 = (K > 1) && (rb_max1[rb >> 5] <= c_min1);
-        if (!dead) {
-            // Dropping a compare needs its own copy of the unrolled loop; copies are only worth their
-            // instruction-cache footprint where they save a sizeable share of the work: not near the
-            // diagonal (uid test active, rare) and not for many objectives.
-            if (need_uid) {
-                EVOXB_TRI_BLOCK(true, 0)
-            } else if (K > 5) {
-                EVOXB_TRI_BLOCK(false, 0)
-            } else {
-                if (sure1) { if (sure2) EVOXB_TRI_BLOCK(false, 3) else EVOXB_TRI_BLOCK(false, 1) }
-                else       { if (sure2) EVOXB_TRI_BLOCK(false, 2) else EVOXB_TRI_BLOCK(false, 0) }
-            }
-        }
-        const int64_t r = tile_row0 + rb + lane;
-        if (r < n_rows) *reinterpret_cast<uint4 *>((kPacked ? D + rows.vstart(r) * 4 + word_base : D + r * rows.row_words + word_base)) = v;
-    }
-#undef EVOXB_TRI_BLOCK
+template <int M, bool kPacked>
+__device__ __forceinline__ void build_tri_tile(const float *__restrict__ xt, int64_t npad, int64_t n_rows,
+                                               const int *__restrict__ uid_row, const int *__restrict__ uid_col,
+                                               const float *__restrict__ tile_min1, const float *__restrict__ tile_max1,
+                                               uint32_t *__restrict__ D, const TriRows &rows, const TriGrid &g, long long bx,
+                                               int by) {
+#define EVOXB_BX bx
+#define EVOXB_BY by
+#include "dominance_tri_body.cuh"
+#undef EVOXB_BX
+#undef EVOXB_BY
 }
 
 // cm == nullptr: the whole matrix on one GPU.  Otherwise only the column chunks of *cm are built and a
@@ -408,6 +292,298 @@ inline int launch_dominance_build_tri(const float *xt, int64_t npad, int64_t n_r
 #undef EVOXB_TRI_CASE
     EVOXB_LAUNCH_CHECK("dominance_build_tri_kernel");
     return 0;
+}
+
+// The same tiles from a small persistent grid, run only when *go is set: the exact float kernel as the fall-back of
+// the level build below (both are enqueued; the flag is decided on the device).
+template <int M, bool kPacked>
+__global__ void __launch_bounds__(kBuildThreads)
+dominance_build_tri_fallback_kernel(const float *__restrict__ xt, int64_t npad, int64_t n_rows,
+                                    const int *__restrict__ uid_row, const int *__restrict__ uid_col,
+                                    const float *__restrict__ tile_min1, const float *__restrict__ tile_max1,
+                                    uint32_t *__restrict__ D, TriRows rows, TriGrid g, long long gx, int gy,
+                                    const int *__restrict__ go) {
+    if (*go == 0) return;
+    const long long total = gx * gy;
+    for (long long t = blockIdx.x; t < total; t += gridDim.x) {
+        build_tri_tile<M, kPacked>(xt, npad, n_rows, uid_row, uid_col, tile_min1, tile_max1, D, rows, g, t % gx, (int)(t / gx));
+        __syncthreads();  // the tile's shared arrays are reused by the next one
+    }
+}
+
+inline int launch_dominance_build_tri_fallback(const float *xt, int64_t npad, int64_t n_rows, int m, const int *uid_row,
+                                               const int *uid_col, const float *tile_min1, const float *tile_max1,
+                                               uint32_t *D, TriRows rows, TriGrid g, long long gx, int gy, const int *go,
+                                               cudaStream_t s) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned grid = (unsigned)(sms * 5);  // five CTAs of 256 threads per SM, as the one-tile-per-CTA launch reaches
+#define EVOXB_TRI_CASE(MM)                                                                                          \
+    case MM:                                                                                                        \
+        if (rows.tri)                                                                                               \
+            dominance_build_tri_fallback_kernel<MM, true><<<grid, kBuildThreads, 0, s>>>(                           \
+                xt, npad, n_rows, uid_row, uid_col, tile_min1, tile_max1, D, rows, g, gx, gy, go);                  \
+        else                                                                                                        \
+            dominance_build_tri_fallback_kernel<MM, false><<<grid, kBuildThreads, 0, s>>>(                          \
+                xt, npad, n_rows, uid_row, uid_col, tile_min1, tile_max1, D, rows, g, gx, gy, go);                  \
+        break;
+    switch (m) {
+        EVOXB_TRI_CASE(2) EVOXB_TRI_CASE(3) EVOXB_TRI_CASE(4) EVOXB_TRI_CASE(5) EVOXB_TRI_CASE(6)
+        EVOXB_TRI_CASE(7) EVOXB_TRI_CASE(8) EVOXB_TRI_CASE(9) EVOXB_TRI_CASE(10) EVOXB_TRI_CASE(11) EVOXB_TRI_CASE(12)
+        EVOXB_TRI_CASE(13) EVOXB_TRI_CASE(14) EVOXB_TRI_CASE(15) EVOXB_TRI_CASE(16)
+        default:
+            return fail(EVOXB_E_UNSUPPORTED, "presorted build supports 2 <= m <= 16 here (got %d)", m);
+    }
+#undef EVOXB_TRI_CASE
+    EVOXB_LAUNCH_CHECK("dominance_build_tri_fallback_kernel");
+    return 0;
+}
+
+// ---- K1, level form ------------------------------------------------------------------------------
+// Objectives 1..M-1 are replaced by 15-bit LEVELS (levels.cuh): a monotone map of the float order, so
+// x_ik <= x_jk implies level_ik <= level_jk.  Two levels share a 32-bit word, bit 15 of each half is a guard bit
+// that the column side sets: (column word - row word) keeps a guard bit iff that half's row level <= the column's
+// (a borrow out of a failing half can only make a higher half fail too, and the product is an AND anyway).  Per 32
+// pairs the inner loop is W = ceil((M-1)/2) IMAD (FMA pipe) + the ANDs + one LOP3 with predicate output + VOTE
+// instead of M-1 FSETP + VOTE on the ALU pipe alone: twice the pairs per clock at M = 5 (measured).  The result is
+// a superset of the dominance relation; the pairs that share a level in some objective but compare the other way
+// as floats are cleared afterwards by level_fixup_kernel.  Rows / columns with a NaN are rejected by the uid test
+// exactly as in the float kernel.
+constexpr uint32_t kLvlGuard = 0x80008000u;
+
+// bad = some guard bit of (t & dl) is missing; returns the ballot of the pairs that pass
+__device__ __forceinline__ uint32_t lvl_ballot(uint32_t t, uint32_t dl) {
+    uint32_t b, dummy;
+    asm("{ .reg .pred p, q;\n"
+        "setp.eq.u32 q, 0, 0;\n"
+        "lop3.and.b32 %1|p, %2, %3, 0x80008000, 0x2a, q;\n"
+        "vote.sync.ballot.b32 %0, !p, 0xffffffff; }"
+        : "=r"(b), "=r"(dummy)
+        : "r"(t), "r"(dl));
+    return b;
+}
+__device__ __forceinline__ uint32_t lvl_ballot_uid(uint32_t t, uint32_t dl, int ui, int uj) {
+    uint32_t b, dummy;
+    asm("{ .reg .pred p, q, r;\n"
+        "setp.eq.u32 q, 0, 0;\n"
+        "lop3.and.b32 %1|p, %2, %3, 0x80008000, 0x2a, q;\n"
+        "setp.lt.and.s32 r, %4, %5, !p;\n"
+        "vote.sync.ballot.b32 %0, r, 0xffffffff; }"
+        : "=r"(b), "=r"(dummy)
+        : "r"(t), "r"(dl), "r"(ui), "r"(uj));
+    return b;
+}
+
+template <int W>
+struct LvlCfg {
+    // row words padded to a power of two so that a row is one vector load from shared memory
+    static constexpr int kPad = W <= 1 ? 1 : W <= 2 ? 2 : W <= 4 ? 4 : 8;
+    // rows per CTA: as many as keep rows + columns + staging under 48 KB of shared memory
+    static constexpr int kRows = W <= 2 ? 1024 : W <= 4 ? 512 : W <= 6 ? 256 : 128;
+    static constexpr int kRowTiles = kRows / kTileRows;  // 128-row tiles per CTA
+    static constexpr int kBlocks = kRows / 32;
+};
+
+__host__ __device__ inline long long lvl_groups_before_band(int b, int ntc, int row_tiles) {
+    return tri_tiles_before_band(b, ntc) / row_tiles;  // a band holds 32 row tiles: divisible by 8, 4, 2, 1
+}
+
+// CTAs of the one-GPU launch
+inline long long lvl_total_groups(const TriGrid &g, int row_tiles) {
+    const int last = g.nbands - 1;
+    return lvl_groups_before_band(last, g.ntc, row_tiles) +
+           (long long)((g.nrt - 32 * last + row_tiles - 1) / row_tiles) * (g.ntc - 4 * last);
+}
+
+// A CTA takes kRows consecutive rows (inside one 1024-tile, hence one band of x_1) against one 1024-column tile.
+// Rows and columns are staged in shared memory once; the work is then cut into items of 32 rows x 128 columns
+// (one x_2 band of rows against one x_2 band of columns) that the eight warps draw from a counter in shared
+// memory.  No barrier after the prologue: the items differ a lot in cost (dead, one word dropped, full, with uid
+// test) and a static split by columns left the warps of the low-x_2 columns idle (ncu: 27 % of the issue slots
+// lost, the largest stall reason the barrier).
+template <int W, bool kPacked>
+__global__ void __launch_bounds__(kBuildThreads)
+dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t n_rows, const int *__restrict__ uid_row,
+                           const int *__restrict__ uid_col, const float *__restrict__ tile_min1,
+                           const float *__restrict__ tile_max1, uint32_t *__restrict__ D, TriRows rows, TriGrid g,
+                           const int *__restrict__ fallback) {
+    using Cfg = LvlCfg<W>;
+    constexpr int WP = Cfg::kPad, R = Cfg::kRows, NB = Cfg::kBlocks;
+    __shared__ __align__(16) uint32_t qs[R][WP];          // row level words
+    __shared__ int us[R];                                 // row uids
+    __shared__ uint32_t qc[W][kTileCols];                 // column level words, guard bits set
+    __shared__ int uc[kTileCols];                         // column uids
+    __shared__ __align__(16) uint32_t stage[kBuildThreads / 32][32][kC];
+    __shared__ int rb_min2[NB], rb_max2[NB], rb_umax[NB];  // per 32-row block: band of objective 2's level, largest uid
+    __shared__ int oc_min2[8], oc_max2[8], oc_umin[8];     // per 128 columns
+    __shared__ int next_item;
+    if (*fallback) return;  // the levels are too coarse for this population: the float kernel runs instead
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+
+    int rt0, ct;
+    int64_t word0;  // word offset of the tile's first column inside a (local) matrix row
+    if (g.sharded) {
+        const int lct = blockIdx.x, lc = lct >> 2, c = g.cm.global(lc);
+        rt0 = blockIdx.y * Cfg::kRowTiles;
+        if (c < (rt0 >> 5)) return;  // chunk entirely left of the rows' own chunk: never read by the peel
+        ct = c * 4 + (lct & 3);
+        word0 = (int64_t)lct * (kTileCols / 32);
+    } else {
+        const long long t = blockIdx.x;
+        int lo = 0, hi = g.nbands;  // before(lo) <= t < before(hi)
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (lvl_groups_before_band(mid, g.ntc, Cfg::kRowTiles) <= t) lo = mid; else hi = mid;
+        }
+        const int band = lo;
+        const int width = g.ntc - 4 * band;
+        const long long local = t - lvl_groups_before_band(band, g.ntc, Cfg::kRowTiles);
+        rt0 = 32 * band + Cfg::kRowTiles * (int)(local / width);
+        ct = 4 * band + (int)(local % width);
+        word0 = (int64_t)ct * (kTileCols / 32);
+    }
+    const int64_t row0 = (int64_t)rt0 * kTileRows;
+    const int64_t col0 = (int64_t)ct * kTileCols;
+    // tile-level test on objective 1 (floats, as in the float kernel): the CTA's rows lie in one 1024-tile
+    const int rt1024 = (int)(row0 / kTileCols);
+    const float r_lo = tile_min1[rt1024], r_hi = tile_max1[rt1024];
+    const float c_lo = tile_min1[ct], c_hi = tile_max1[ct];
+    if (r_lo > c_hi) return;  // never fetched by the readers (see dominance_tri_body.cuh): nothing to write
+    const bool sure1 = r_hi <= c_lo;
+    const int nb = (int)min((int64_t)NB, (n_rows - row0 + 31) / 32);  // 32-row blocks that hold a row
+
+    for (int t = threadIdx.x; t < R * W; t += kBuildThreads) {
+        const int w = t / R, r = t - w * R;
+        qs[r][w] = (row0 + r < n_rows) ? q[(int64_t)w * npad + row0 + r] : 0u;
+    }
+    for (int r = threadIdx.x; r < R; r += kBuildThreads) us[r] = (row0 + r < n_rows) ? uid_row[row0 + r] : 0x7fffffff;
+    for (int t = threadIdx.x; t < kTileCols * W; t += kBuildThreads) {
+        const int w = t / kTileCols, j = t - w * kTileCols;
+        qc[w][j] = q[(int64_t)w * npad + col0 + j] | kLvlGuard;
+    }
+    for (int j = threadIdx.x; j < kTileCols; j += kBuildThreads) uc[j] = uid_col[col0 + j];
+    if (threadIdx.x == 0) next_item = 0;
+    __syncthreads();
+    // bands: warp w reduces row blocks w, w + 8, ... and the columns of octile w.  The band of objective 2 is the
+    // high half of word 0 (only meaningful when M >= 3; a padding half is 0 on both sides).
+    for (int b = warp; b < NB; b += kBuildThreads / 32) {
+        int lo = (int)(qs[b * 32 + lane][0] >> 16), hi = lo, um = us[b * 32 + lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+            um = max(um, __shfl_xor_sync(0xffffffffu, um, o));
+        }
+        if (lane == 0) {
+            rb_min2[b] = lo;
+            rb_max2[b] = hi;
+            rb_umax[b] = um;
+        }
+    }
+    {
+        int lo = 0x7fff, hi = 0, um = 0x7fffffff;
+#pragma unroll
+        for (int c = 0; c < kC; ++c) {
+            const int v = (int)(qc[0][warp * 128 + c * 32 + lane] >> 16) & 0x7fff;
+            lo = min(lo, v);
+            hi = max(hi, v);
+            um = min(um, uc[warp * 128 + c * 32 + lane]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+            um = min(um, __shfl_xor_sync(0xffffffffu, um, o));
+        }
+        if (lane == 0) {
+            oc_min2[warp] = lo;
+            oc_max2[warp] = hi;
+            oc_umin[warp] = um;
+        }
+    }
+    __syncthreads();
+    uint32_t(*st)[kC] = stage[warp];
+
+    // One 32-row block against 128 columns.  FIRST = 1: word 0 (objectives 1 and 2) is known to pass for every
+    // pair of the block and is left out.
+#define EVOXB_LVL_BLOCK(WITH_UID, FIRST)                                                                   \
+    {                                                                                                       \
+        _Pragma("unroll 4") for (int ii = 0; ii < 32; ++ii) {                                               \
+            uint32_t a[WP];                                                                                 \
+            if (WP == 1) a[0] = qs[rb + ii][0];                                                             \
+            else if (WP == 2) { const uint2 v2 = *reinterpret_cast<const uint2 *>(qs[rb + ii]); a[0] = v2.x; a[1] = v2.y; } \
+            else {                                                                                          \
+                _Pragma("unroll") for (int h = 0; h < WP / 4; ++h) {                                        \
+                    const uint4 v4 = *reinterpret_cast<const uint4 *>(&qs[rb + ii][4 * h]);                 \
+                    a[4 * h] = v4.x; a[4 * h + 1] = v4.y; a[4 * h + 2] = v4.z; a[4 * h + 3] = v4.w;         \
+                }                                                                                           \
+            }                                                                                               \
+            const int ui = WITH_UID ? us[rb + ii] : 0;                                                      \
+            uint32_t b[kC];                                                                                 \
+            _Pragma("unroll") for (int c = 0; c < kC; ++c) {                                                \
+                constexpr int F = (FIRST) && W > 1 ? 1 : 0;                                                 \
+                uint32_t t = xj[c][F] - a[F];                                                               \
+                _Pragma("unroll") for (int w = F + 1; w < W - 1; ++w) t &= xj[c][w] - a[w];                 \
+                const uint32_t dl = (W - 1 > F) ? xj[c][W - 1] - a[W - 1] : t;                              \
+                b[c] = WITH_UID ? lvl_ballot_uid(t, dl, ui, uj[c]) : lvl_ballot(t, dl);                     \
+            }                                                                                               \
+            if (lane == 0) *reinterpret_cast<uint4 *>(st[ii]) = make_uint4(b[0], b[1], b[2], b[3]);         \
+        }                                                                                                   \
+        __syncwarp();                                                                                       \
+        v = *reinterpret_cast<const uint4 *>(st[lane]);                                                     \
+        __syncwarp();                                                                                       \
+    }
+
+    // An item is one 32-row block against 256 columns (two octiles, done one after the other): a lane then owns a
+    // whole 32-byte sector of its row, so no sector is written in two halves at different times (which costs a
+    // read-modify-write in DRAM once the first half has left the L2).  Column pair 3 first: the high-x_2 columns
+    // have the most live row blocks.
+    uint32_t xj[kC][W];
+    int uj[kC];
+    const int total = 4 * nb;
+    for (;;) {
+        int item = 0;
+        if (lane == 0) item = atomicAdd(&next_item, 1);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= total) break;
+        const int pair = 3 - item / nb, blk = item - (3 - pair) * nb;
+        const int rb = blk * 32;
+        uint4 out0 = make_uint4(0u, 0u, 0u, 0u), out1 = out0;
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+            const int oct = pair * 2 + h;
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            const int c_min2 = oc_min2[oct], c_max2 = oc_max2[oct];
+            const bool dead = rb_min2[blk] > c_max2;    // no pair of the block passes objective 2
+            const bool sure2 = rb_max2[blk] <= c_min2;  // every pair passes it
+            if (!dead) {
+#pragma unroll
+                for (int c = 0; c < kC; ++c) {
+                    uj[c] = uc[oct * 128 + c * 32 + lane];
+#pragma unroll
+                    for (int w = 0; w < W; ++w) xj[c][w] = qc[w][oct * 128 + c * 32 + lane];
+                }
+                if (!(rb_umax[blk] < oc_umin[oct])) {
+                    EVOXB_LVL_BLOCK(true, 0)
+                } else if (W > 1 && sure1 && sure2) {
+                    EVOXB_LVL_BLOCK(false, 1)
+                } else {
+                    EVOXB_LVL_BLOCK(false, 0)
+                }
+            }
+            if (h == 0) out0 = v; else out1 = v;
+        }
+        const int64_t r = row0 + rb + lane;
+        const int64_t wb = word0 + pair * 2 * kC;
+        if (r < n_rows) {
+            uint4 *dst = reinterpret_cast<uint4 *>((kPacked ? D + rows.vstart(r) * 4 + wb : D + r * rows.row_words + wb));
+            dst[0] = out0;
+            dst[1] = out1;
+        }
+    }
+#undef EVOXB_LVL_BLOCK
 }
 
 // ---- a2: dense boolean relation between two different sets (utils/common.py:101-104) ----------

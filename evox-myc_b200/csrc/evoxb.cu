@@ -18,6 +18,7 @@
 #include "variation.cuh"
 #include "tail.cuh"
 #include "nsga3.cuh"
+#include "levels.cuh"
 
 namespace evoxb {
 
@@ -78,10 +79,25 @@ struct NdsLayout {
     int *totals;          // front sizes of the current batch of fronts
     int *cnt;             // members per region of the current front
     unsigned char *flow_ring;  // single-GPU exchange buffer of the data-flow peel (peel_flow.cuh)
+    bool levels;               // the level form of K1 is used (levels.cuh)
+    LevelBufs lv;
     size_t bytes;
 };
 
 static bool nds_use_tri(int m) { return m <= 16; }
+
+// Which form of K1 builds the matrix of a presorted population: "levels" = the level kernel wherever it exists
+// (m >= 2), "exact" = the float kernel, unset = by size.  Read on every call (tests switch it in-process).
+// The levels pay where the build is long enough to absorb their set-up (about 0.1 ms of small kernels) and
+// compares are many per pair: m >= 4 from 65536 rows on (measured on the B200).
+static bool nds_use_levels(int64_t n, int m) {
+    if (!nds_use_tri(m) || m < 2 || n <= 0) return false;
+    if (const char *ev = getenv("EVOXB_BUILD_MODE")) {
+        if (!strcmp(ev, "levels")) return true;
+        if (!strcmp(ev, "exact")) return false;
+    }
+    return m >= 4 && n >= 65536;
+}
 
 
 constexpr int kFrontBatch = 4;  // fronts enqueued between two host checks of "front empty?" (multi-GPU)
@@ -125,6 +141,24 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         L.cnt = c.take<int>(kMaxChunks);
     }
     L.flow_ring = c.take<unsigned char>(flow_ring_bytes(L.npad / 32));
+    L.levels = L.tri && nds_use_levels(n, m);
+    if (L.levels) {
+        LevelBufs &v = L.lv;
+        v.K = m - 1;
+        v.W = (v.K + 1) / 2;
+        v.q = c.take<uint32_t>((size_t)v.W * (size_t)L.npad);
+        const size_t zwords = (size_t)v.K * (kLvlBins + 2 * (size_t)kLvlCount);
+        v.zero0 = c.take<uint32_t>(zwords);
+        v.zero_bytes = zwords * sizeof(uint32_t);
+        v.hist1 = v.zero0;
+        v.cnt = v.hist1 + (size_t)v.K * kLvlBins;
+        v.kmax = v.cnt + (size_t)v.K * kLvlCount;
+        v.kmin = c.take<uint32_t>((size_t)v.K * kLvlCount);
+        v.bins = c.take<uint2>((size_t)v.K * kLvlBins);
+        v.start = c.take<uint32_t>((size_t)v.K * (kLvlCount + 1));
+        v.cursor = c.take<uint32_t>((size_t)v.K * kLvlCount);
+        v.items = c.take<int2>((size_t)v.K * (size_t)L.npad);
+    }
     // Only the triangle of the presorted matrix is ever written or read.  Storing just that (TriRows) halves
     // the workspace, but measured on the B200 it costs time: the build kernel's stores are 8-10 % slower with
     // the dense rows (c4: 4.38 -> 4.8 ms) and the variable row stride adds address arithmetic to every staged
@@ -359,6 +393,77 @@ static int run_presort(const float *fitness, int64_t n, int m, const NdsLayout &
     return 0;
 }
 
+// K1 in level form (levels.cuh): levels, level kernel, float kernel as the on-device fall-back, fix-up.
+// cm == nullptr: the whole matrix on this GPU.
+template <int W>
+static int run_level_build_w(const NdsLayout &L, int64_t n, int m, cudaStream_t s, const ChunkMap *cm) {
+    const LevelBufs &v = L.lv;
+    const int npad = (int)L.npad, nn = (int)n;
+    int *fallback = &L.ctrl->level_fallback;  // zeroed with the rest of PeelCtrl
+    EVOXB_CUDA(cudaMemsetAsync(v.zero0, 0, v.zero_bytes, s));
+    EVOXB_CUDA(cudaMemsetAsync(v.kmin, 0xff, sizeof(uint32_t) * (size_t)v.K * kLvlCount, s));
+    const unsigned pos_blocks = (unsigned)div_up(L.npad, 256);
+    unsigned hist_blocks = (unsigned)div_up(n, 2048);
+    if (hist_blocks > 296u) hist_blocks = 296u;
+    level_hist_kernel<<<dim3(hist_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, npad, nn, v.hist1);
+    EVOXB_LAUNCH_CHECK("level_hist_kernel");
+    level_plan_kernel<<<(unsigned)v.K, 1024, 0, s>>>(v.hist1, v.bins);
+    EVOXB_LAUNCH_CHECK("level_plan_kernel");
+    level_assign_kernel<W><<<pos_blocks, 256, 0, s>>>(L.xt, npad, nn, v.K, v.bins, v.q, v.cnt, v.kmin, v.kmax);
+    EVOXB_LAUNCH_CHECK("level_assign_kernel");
+    level_scan_kernel<<<(unsigned)v.K, 1024, 0, s>>>(v.cnt, v.kmin, v.kmax, v.start, v.cursor, nn, fallback);
+    EVOXB_LAUNCH_CHECK("level_scan_kernel");
+    level_scatter_kernel<<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, v.q, npad, nn, v.kmin, v.kmax, v.cursor, v.items,
+                                                                       fallback);
+    EVOXB_LAUNCH_CHECK("level_scatter_kernel");
+
+    const TriRows rows = make_rows(L);
+    TriGrid g = make_tri_grid(L.npad, n);
+    if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
+    constexpr int kRowTiles = LvlCfg<W>::kRowTiles;
+    dim3 grid((unsigned)lvl_total_groups(g, kRowTiles));  // level kernel: kRowTiles 128-row tiles per CTA
+    long long gx = g.total;                    // float fall-back: one tile per loop iteration
+    int gy = 1;
+    if (cm) {
+        g.sharded = 1;
+        g.cm = *cm;
+        if (cm->nlocal <= 0) return 0;
+        if (g.nrt > 65535) return fail(EVOXB_E_UNSUPPORTED, "too many row tiles (%d)", g.nrt);
+        grid = dim3((unsigned)(cm->nlocal * 4), (unsigned)div_up(g.nrt, kRowTiles));
+        gx = cm->nlocal * 4;
+        gy = g.nrt;
+    }
+    if (rows.tri)
+        dominance_build_lvl_kernel<W, true><<<grid, kBuildThreads, 0, s>>>(v.q, L.npad, n, L.uid_row, L.uid_col, L.tile_min1,
+                                                                          L.tile_max1, L.D, rows, g, fallback);
+    else
+        dominance_build_lvl_kernel<W, false><<<grid, kBuildThreads, 0, s>>>(v.q, L.npad, n, L.uid_row, L.uid_col, L.tile_min1,
+                                                                           L.tile_max1, L.D, rows, g, fallback);
+    EVOXB_LAUNCH_CHECK("dominance_build_lvl_kernel");
+    if (int rc = launch_dominance_build_tri_fallback(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D,
+                                                     rows, g, gx, gy, fallback, s))
+        return rc;
+    level_fixup_kernel<W><<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, v.q, npad, nn, v.kmin, v.kmax, v.start, v.items,
+                                                                        L.uid_row, L.uid_col, L.D, rows,
+                                                                        cm ? *cm : ChunkMap{0, 1, L.nchunks}, fallback);
+    EVOXB_LAUNCH_CHECK("level_fixup_kernel");
+    return 0;
+}
+
+static int run_level_build(const NdsLayout &L, int64_t n, int m, cudaStream_t s, const ChunkMap *cm = nullptr) {
+    switch (L.lv.W) {
+        case 1: return run_level_build_w<1>(L, n, m, s, cm);
+        case 2: return run_level_build_w<2>(L, n, m, s, cm);
+        case 3: return run_level_build_w<3>(L, n, m, s, cm);
+        case 4: return run_level_build_w<4>(L, n, m, s, cm);
+        case 5: return run_level_build_w<5>(L, n, m, s, cm);
+        case 6: return run_level_build_w<6>(L, n, m, s, cm);
+        case 7: return run_level_build_w<7>(L, n, m, s, cm);
+        case 8: return run_level_build_w<8>(L, n, m, s, cm);
+    }
+    return fail(EVOXB_E_UNSUPPORTED, "level build supports m <= 16 (got %d)", m);
+}
+
 // Enqueues the whole ranking (K0..K3) on `s`.  `L` must come from nds_layout(ws, n, m, n).
 static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const NdsLayout &L, cudaStream_t s,
                    Profiler &prof) {
@@ -372,7 +477,11 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
         if (int rc = run_presort(fitness, n, m, L, s)) return rc;
         perm = L.perm;
         prof.mark("dominance_build", s);
-        if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, make_rows(L), s)) return rc;
+        if (L.levels) {
+            if (int rc = run_level_build(L, n, m, s)) return rc;
+        } else if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, make_rows(L), s)) {
+            return rc;
+        }
     } else {
         transpose_pad_kernel<<<(unsigned)div_up(L.npad, 256), 256, 0, s>>>(fitness, n, m, L.npad, L.xt);
         EVOXB_LAUNCH_CHECK("transpose_pad_kernel");
@@ -511,7 +620,11 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
     if (int rc = run_presort(fitness, n, m, L, s)) return rc;
 
     prof.mark("dominance_build", s);
-    if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, make_rows(L), s, &L.cm)) return rc;
+    if (L.levels) {
+        if (int rc = run_level_build(L, n, m, s, &L.cm)) return rc;
+    } else if (int rc = launch_dominance_build_tri(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D, make_rows(L), s, &L.cm)) {
+        return rc;
+    }
 
     const void *p2p_kern = L.nchunks <= 32    ? (const void *)peel_p2p_kernel<1>
                            : L.nchunks <= 128 ? (const void *)peel_p2p_kernel<4>
@@ -851,6 +964,23 @@ EVOXB_API int evoxb_nds_rank_f32(const float *fitness, int64_t n, int m, int32_t
     prof.begin();
     if (int rc = run_nds(fitness, n, m, rank, L, s, prof)) return rc;
     prof.mark("end", s);
+    return 0;
+}
+
+EVOXB_API int evoxb_nds_build_path(const void *ws, int64_t n, int m, evoxb_stream_t stream, int *path) {
+    if (!path) return fail(EVOXB_E_INVALID, "path is null");
+    if (int rc = check_common((const void *)1, n, m)) return rc;
+    *path = 0;
+    if (n == 0 || !nds_use_tri(m) || !nds_use_levels(n, m)) return 0;
+    if (!ws) {  // host-side answer only: the levels would be used for this shape
+        *path = 1;
+        return 0;
+    }
+    int flag = 0;  // PeelCtrl is the first block of every ranking workspace
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    EVOXB_CUDA(cudaMemcpyAsync(&flag, &static_cast<const PeelCtrl *>(ws)->level_fallback, sizeof(int), cudaMemcpyDeviceToHost, s));
+    EVOXB_CUDA(cudaStreamSynchronize(s));
+    *path = flag ? 2 : 1;
     return 0;
 }
 

@@ -1,0 +1,282 @@
+// Levels for the level form of K1 (dominance.cuh: dominance_build_lvl_kernel) and the fix-up that makes it exact.
+//
+// Replaces nothing of the reference by itself: it is a faster evaluation of `dominate_relation`
+// (src/evox/utils/common.py:95-104) for the presorted population.  Every objective k >= 1 is mapped to a 15-bit
+// level by a monotone function of the float order (-0 == +0, NaN excluded):
+//   order key (sort.cuh: float_to_key) -> first-level bin = its top 12 bits (sign, exponent, 3 mantissa bits);
+//   a histogram over the bins gives every non-empty bin a share of the 32768 levels in proportion to its rows
+//   (at least one); inside a bin the level grows linearly with the remaining 20 key bits.
+// x_ik <= x_jk  =>  level_ik <= level_jk, so "all levels <=" is a superset of "all floats <="; the two differ only
+// for pairs that share a level in some objective and have x_ik > x_jk there.  Those pairs are enumerated from a
+// counting sort of the rows by (objective, level) and their bits cleared with atomicAnd (level_fixup_kernel).
+// Levels whose rows all hold the same value ("pure", e.g. integer-valued or heavily tied objectives) need no
+// fix-up and cost nothing.  If the mixed levels are too crowded for that to be cheap (values packed far more
+// densely than 32768 levels can resolve), a flag is raised on the device and the float kernel runs instead.
+#pragma once
+
+#include "common.cuh"
+#include "dominance.cuh"
+#include "peel.cuh"
+#include "sort.cuh"
+
+namespace evoxb {
+
+constexpr int kLvlBins = 4096;
+constexpr int kLvlCount = 32768;
+constexpr int kLvlSpare = kLvlCount - kLvlBins;  // levels handed out in proportion; every non-empty bin gets >= 1 on top
+constexpr int kLvlMaxBucket = 512;               // a mixed level with more rows than this -> float kernel
+constexpr int kLvlBudgetPerRow = 64;             // sum over mixed levels of rows^2 <= this * n, per objective
+
+struct LevelBufs {
+    int K, W;           // compared objectives (m - 1) and packed words per row
+    uint32_t *q;        // [W][npad] level words, row form (guard bits clear); objective 2w+1 low half, 2w+2 high half
+    uint32_t *zero0;    // start of the region cleared before every call: hist1, cnt, kmax
+    size_t zero_bytes;
+    uint32_t *hist1;    // [K][kLvlBins]
+    uint32_t *cnt;      // [K][kLvlCount] rows per level
+    uint32_t *kmax;     // [K][kLvlCount] largest key of the level
+    uint32_t *kmin;     // [K][kLvlCount] smallest key (set to all ones before every call)
+    uint2 *bins;        // [K][kLvlBins] {first level, levels} of a bin
+    uint32_t *start;    // [K][kLvlCount + 1] first slot of a level in items
+    uint32_t *cursor;   // [K][kLvlCount]
+    int2 *items;        // [K][npad] (position, float bits) grouped by level (mixed levels only)
+};
+
+__device__ __forceinline__ uint32_t level_of(uint32_t key, const uint2 *__restrict__ bins_k) {
+    const uint2 b = __ldg(bins_k + (key >> 20));
+    return b.x + __umulhi((key & 0xfffffu) << 12, b.y);
+}
+
+// Rows per first-level bin.  grid = (CTAs, K)
+__global__ void __launch_bounds__(256)
+level_hist_kernel(const float *__restrict__ xt, int npad, int n, uint32_t *__restrict__ hist1) {
+    __shared__ uint32_t h[kLvlBins];
+    const int k = blockIdx.y;
+    for (int i = threadIdx.x; i < kLvlBins; i += 256) h[i] = 0u;
+    __syncthreads();
+    const float *x = xt + (int64_t)(k + 1) * npad;
+    for (int p = blockIdx.x * 256 + threadIdx.x; p < n; p += gridDim.x * 256) {
+        const uint32_t key = float_to_key(x[p]);
+        if (key != 0xffffffffu) atomicAdd(&h[key >> 20], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < kLvlBins; i += 256)
+        if (h[i]) atomicAdd(&hist1[k * kLvlBins + i], h[i]);
+}
+
+// Block-wide exclusive scan of one value per thread (1024 threads); returns the exclusive prefix, *total = sum.
+__device__ __forceinline__ uint32_t block_scan_1024(uint32_t v, uint32_t *sh_warp, uint32_t *total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    __syncthreads();
+    if (lane == 31) sh_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = sh_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        sh_warp[lane] = wi - w;
+        if (lane == 31) sh_warp[32] = wi;
+    }
+    __syncthreads();
+    *total = sh_warp[32];
+    return sh_warp[warp] + incl - v;
+}
+
+// Levels per bin and their first level.  One CTA of 1024 threads per objective, 4 bins per thread.
+__global__ void __launch_bounds__(1024) level_plan_kernel(const uint32_t *__restrict__ hist1, uint2 *__restrict__ bins) {
+    __shared__ uint32_t sh_warp[33];
+    const int k = blockIdx.x;
+    uint32_t h[4], rows = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        h[e] = hist1[k * kLvlBins + threadIdx.x * 4 + e];
+        rows += h[e];
+    }
+    uint32_t total;
+    block_scan_1024(rows, sh_warp, &total);
+    uint32_t ns[4], mine = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        ns[e] = h[e] ? 1u + (uint32_t)(((unsigned long long)h[e] * kLvlSpare) / total) : 0u;
+        mine += ns[e];
+    }
+    uint32_t levels;
+    uint32_t base = block_scan_1024(mine, sh_warp, &levels);
+    // sum <= kLvlSpare + non-empty bins <= kLvlCount
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        bins[k * kLvlBins + threadIdx.x * 4 + e] = make_uint2(base, ns[e]);
+        base += ns[e];
+    }
+}
+
+// Level words of every position; rows, smallest and largest key per level.  One thread per position.
+template <int W>
+__global__ void __launch_bounds__(256)
+level_assign_kernel(const float *__restrict__ xt, int npad, int n, int K, const uint2 *__restrict__ bins,
+                    uint32_t *__restrict__ q, uint32_t *__restrict__ cnt, uint32_t *__restrict__ kmin,
+                    uint32_t *__restrict__ kmax) {
+    const int p = blockIdx.x * 256 + threadIdx.x;
+    if (p >= npad) return;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+        uint32_t word = 0u;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            const int k = 2 * w + hh;  // objective k + 1
+            if (k < K && p < n) {
+                const uint32_t key = float_to_key(xt[(int64_t)(k + 1) * npad + p]);
+                if (key != 0xffffffffu) {
+                    const uint32_t lv = level_of(key, bins + k * kLvlBins);
+                    word |= lv << (16 * hh);
+                    atomicAdd(&cnt[k * kLvlCount + lv], 1u);
+                    atomicMin(&kmin[k * kLvlCount + lv], key);
+                    atomicMax(&kmax[k * kLvlCount + lv], key);
+                }
+            }
+        }
+        q[(int64_t)w * npad + p] = word;
+    }
+}
+
+// First slot of every level (exclusive scan of the rows per level), and the decision whether the fix-up is
+// affordable.  One CTA of 1024 threads per objective; the 32768 levels go through shared memory in four pieces of
+// 8192 so that every global access is coalesced (thread t owns 8 consecutive levels of a piece for the scan).
+constexpr int kLvlPiece = 8192;
+__global__ void __launch_bounds__(1024)
+level_scan_kernel(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ kmin, const uint32_t *__restrict__ kmax,
+                  uint32_t *__restrict__ start, uint32_t *__restrict__ cursor, int n, int *__restrict__ fallback) {
+    __shared__ uint32_t sh[kLvlPiece];
+    __shared__ uint32_t sh_warp[33];
+    __shared__ unsigned long long sh_cost;
+    __shared__ uint32_t sh_big;
+    const int k = blockIdx.x, t = threadIdx.x;
+    if (t == 0) {
+        sh_cost = 0ull;
+        sh_big = 0u;
+    }
+    uint32_t big = 0, carry = 0;
+    unsigned long long cost = 0;
+    for (int piece = 0; piece < kLvlCount / kLvlPiece; ++piece) {
+        const int i0 = k * kLvlCount + piece * kLvlPiece;
+#pragma unroll
+        for (int j = 0; j < kLvlPiece / 1024; ++j) {
+            const int i = i0 + j * 1024 + t;
+            const uint32_t c = cnt[i];
+            sh[j * 1024 + t] = c;
+            if (c > 1 && kmin[i] != kmax[i]) {
+                cost += (unsigned long long)c * c;
+                big = max(big, c);
+            }
+        }
+        __syncthreads();
+        uint32_t v[8], mine = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            v[e] = sh[t * 8 + e];
+            mine += v[e];
+        }
+        uint32_t total;
+        uint32_t base = carry + block_scan_1024(mine, sh_warp, &total);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            sh[t * 8 + e] = base;
+            base += v[e];
+        }
+        carry += total;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < kLvlPiece / 1024; ++j) {
+            const uint32_t st = sh[j * 1024 + t];
+            start[k * (kLvlCount + 1) + piece * kLvlPiece + j * 1024 + t] = st;
+            cursor[i0 + j * 1024 + t] = st;
+        }
+        __syncthreads();
+    }
+    if (t == 0) start[k * (kLvlCount + 1) + kLvlCount] = carry;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cost += __shfl_xor_sync(0xffffffffu, cost, o);
+        big = max(big, __shfl_xor_sync(0xffffffffu, big, o));
+    }
+    if ((t & 31) == 0) {
+        if (cost) atomicAdd(&sh_cost, cost);
+        if (big) atomicMax(&sh_big, big);
+    }
+    __syncthreads();
+    if (t == 0 && (sh_cost > (unsigned long long)kLvlBudgetPerRow * (unsigned long long)n || sh_big > kLvlMaxBucket))
+        atomicExch(fallback, 1);
+}
+
+__device__ __forceinline__ uint32_t level_field(const uint32_t *__restrict__ q, int npad, int k, int p) {
+    return (q[(int64_t)(k >> 1) * npad + p] >> (16 * (k & 1))) & 0x7fffu;
+}
+
+// Positions grouped by level, mixed levels only.  grid = (npad / 256, K)
+__global__ void __launch_bounds__(256)
+level_scatter_kernel(const float *__restrict__ xt, const uint32_t *__restrict__ q, int npad, int n,
+                     const uint32_t *__restrict__ kmin, const uint32_t *__restrict__ kmax, uint32_t *__restrict__ cursor,
+                     int2 *__restrict__ items, const int *__restrict__ fallback) {
+    if (*fallback) return;
+    const int p = blockIdx.x * 256 + threadIdx.x, k = blockIdx.y;
+    if (p >= n) return;
+    const float x = xt[(int64_t)(k + 1) * npad + p];
+    if (x != x) return;
+    const int i = k * kLvlCount + (int)level_field(q, npad, k, p);
+    if (kmin[i] == kmax[i]) return;
+    items[(int64_t)k * npad + atomicAdd(&cursor[i], 1u)] = make_int2(p, __float_as_int(x));
+}
+
+// Clears the bits of the pairs (row i, column j in i's chunk or a later one) that share a level in objective k + 1
+// but have x_ik > x_jk.  Only bits that the level kernel can have set are touched (all other levels <=, uid test),
+// so the atomics stay few.  grid = (npad / 256, K); one thread per (position, objective) walks its level, four
+// members per round so that their loads are in flight together.
+template <int W>
+__global__ void __launch_bounds__(256)
+level_fixup_kernel(const float *__restrict__ xt, const uint32_t *__restrict__ q, int npad, int n,
+                   const uint32_t *__restrict__ kmin, const uint32_t *__restrict__ kmax, const uint32_t *__restrict__ start,
+                   const int2 *__restrict__ items, const int *__restrict__ uid_row, const int *__restrict__ uid_col,
+                   uint32_t *__restrict__ D, TriRows rows, ChunkMap cm, const int *__restrict__ fallback) {
+    if (*fallback) return;
+    const int pi = blockIdx.x * 256 + threadIdx.x, k = blockIdx.y;
+    if (pi >= n) return;
+    const float xi = xt[(int64_t)(k + 1) * npad + pi];
+    if (xi != xi) return;
+    const int lv = (int)level_field(q, npad, k, pi);
+    const int i = k * kLvlCount + lv;
+    if (kmin[i] == kmax[i]) return;
+    const uint32_t s0 = start[k * (kLvlCount + 1) + lv], s1 = start[k * (kLvlCount + 1) + lv + 1];
+    const int2 *it = items + (int64_t)k * npad;
+    const int ci = pi >> 12;
+    for (uint32_t t0 = s0; t0 < s1; t0 += 4) {
+        int2 mem[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) mem[e] = (t0 + e < s1) ? __ldg(it + t0 + e) : make_int2(pi, 0);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int pj = mem[e].x;
+            // i is the row: j must sit in the same chunk (where positions carry no order) or in a later one
+            if (pj == pi || (pj >> 12) < ci) continue;
+            if (!(xi > __int_as_float(mem[e].y))) continue;  // floats agree with the levels: nothing to clear
+            const int off = (pj >> 12) - cm.first;
+            if (off < 0 || off % cm.stride != 0) continue;    // column chunk of another GPU
+            uint32_t d = kLvlGuard;
+#pragma unroll
+            for (int w = 0; w < W; ++w) d &= (q[(int64_t)w * npad + pj] | kLvlGuard) - q[(int64_t)w * npad + pi];
+            if (d != kLvlGuard || !(uid_row[pi] < uid_col[pj])) continue;  // the level kernel left this bit clear
+            const int64_t row_word0 = rows.tri ? rows.vstart(pi) * 4 : (int64_t)pi * rows.row_words;
+            atomicAnd(D + row_word0 + (int64_t)(off / cm.stride) * kChunkWords + ((pj & 4095) >> 5), ~(1u << (pj & 31)));
+        }
+    }
+}
+
+}  // namespace evoxb

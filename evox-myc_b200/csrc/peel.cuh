@@ -59,8 +59,9 @@ constexpr int kStageRows = 1024;  // member rows resolved per staging round
 
 // Band of objective 1 of every 1024-position tile (presort.cuh).  A (row, 1024-column tile) segment of
 // the matrix is all zero when the row tile's smallest x_1 exceeds the column tile's largest -- the
-// build kernel zero-filled it without looking -- so count and peel do not fetch those 128-byte
-// quarters of a row chunk (predicated loads: no branch, the batch stays in flight).
+// build kernels leave it UNWRITTEN on that very test -- so count and peel must not, and do not, fetch those
+// 128-byte quarters of a row chunk (predicated loads: no branch, the batch stays in flight).  Every load of
+// the presorted matrix has to carry this predicate.
 struct TileBands {
     const float *tmin;  // nullptr: no band information (unsorted full-matrix mode)
     const float *tmax;
@@ -386,6 +387,7 @@ struct PeelCtrl {
     int fronts_done;         // number of fronts peeled (written at exit)
     int front0;              // size of front 0 (front0_size_kernel); only set when both peel kernels are enqueued
     int presort_slow;        // raised by the presort when a run of equal key_0 is too long for its fast path
+    int level_fallback;      // raised by level_scan_kernel: the level build is skipped, the float kernel runs (levels.cuh)
 };
 
 // K3: the whole peel loop in one cooperative launch (grid-wide sync twice per front).

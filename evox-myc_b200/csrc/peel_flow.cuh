@@ -377,7 +377,7 @@ __device__ __forceinline__ void flow_piece_pass(const FlowArgs &a, const FlowPie
                 const int i = t + u * kFlowThreads;
                 const int row = sm.rows[qb + (min(i, items - 1) >> lg_parts)];
                 // rows of later chunks have nothing (and nothing defined) in this chunk's columns; a row tile whose
-                // smallest x_1 exceeds the column tile's largest was zero-filled by the build kernel
+                // smallest x_1 exceeds the column tile's largest is all zero and was never written by the build kernel
                 const bool fetch = i < items && (!tri || (row >> 12) <= pc.chunk) && !(sm.tmin[row >> 10] > col_max);
                 v[u] = ldg_stream_v4_if(base + a.rows.vstart(row), fetch);
             }

@@ -53,6 +53,21 @@ def non_dominated_sort(x, method: str = "auto"):
     return rt.give_back(rank, a, "nds_rank")
 
 
+def nds_build_path(n: int, m: int, device=None) -> str:
+    """How the dominance matrix of the last ``non_dominated_sort`` call of this shape was built (no counterpart in
+    the reference; tests and benchmark labels): ``"float"``, ``"levels"`` or ``"levels->float"`` (levels judged too
+    coarse on the device, float kernel ran).  Reads the call's workspace, so ask right after the call."""
+    L = _lib.lib()
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    need = ctypes.c_size_t()
+    _lib.check(L.evoxb_nds_workspace_bytes(n, m, ctypes.byref(need)))
+    ws = rt.workspace(need.value, device)
+    path = ctypes.c_int(0)
+    with torch.cuda.device(device):
+        _lib.check(L.evoxb_nds_build_path(ws.data_ptr(), n, m, rt.stream_ptr(device), ctypes.byref(path)))
+    return ("float", "levels", "levels->float")[path.value]
+
+
 def _ws_call(size_fn, size_args, device):
     need = ctypes.c_size_t()
     _lib.check(size_fn(*size_args, ctypes.byref(need)))

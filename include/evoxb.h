@@ -62,6 +62,13 @@ EVOXB_API int evoxb_dominate_relation_f32(const float *x, int64_t nx, const floa
 EVOXB_API int evoxb_nds_workspace_bytes(int64_t n, int m, size_t *bytes);
 EVOXB_API int evoxb_nds_rank_f32(const float *fitness, int64_t n, int m, int32_t *rank, void *ws,
                        size_t ws_bytes, evoxb_stream_t stream);
+/* How the dominance matrix of the last evoxb_nds_rank_f32 / evoxb_nds_rank_sharded_f32 call on `ws` was built
+ * (no counterpart in the reference; for tests and benchmark labels): 0 = float compares, 1 = 15-bit levels +
+ * fix-up (m >= 4 from 65536 rows on; environment EVOXB_BUILD_MODE=levels|exact overrides), 2 = levels were
+ * prepared but judged too coarse for this population on the device, and the float kernel ran.  The result of
+ * the call is the same in all three.  Synchronises `stream` (one 4-byte copy).  With ws == NULL nothing is
+ * read from the device: path = 1 if the levels would be used for this shape, else 0.                        */
+EVOXB_API int evoxb_nds_build_path(const void *ws, int64_t n, int m, evoxb_stream_t stream, int *path);
 
 /* ---- a5: crowding_distance(costs, mask) -> dist ---------------------------------------------
  * src/evox/operators/selection/non_dominate.py:116-156.  fitness is (n, m) float32; mask is (n)
