@@ -510,7 +510,7 @@ dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t
     // pair of the block and is left out.
 #define EVOXB_LVL_BLOCK(WITH_UID, FIRST)                                                                   \
     {                                                                                                       \
-        _Pragma("unroll 4") for (int ii = 0; ii < 32; ++ii) {                                               \
+        _Pragma("unroll 8") for (int ii = 0; ii < 32; ++ii) {                                               \
             uint32_t a[WP];                                                                                 \
             if (WP == 1) a[0] = qs[rb + ii][0];                                                             \
             else if (WP == 2) { const uint2 v2 = *reinterpret_cast<const uint2 *>(qs[rb + ii]); a[0] = v2.x; a[1] = v2.y; } \

@@ -147,10 +147,13 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         v.K = m - 1;
         v.W = (v.K + 1) / 2;
         v.q = c.take<uint32_t>((size_t)v.W * (size_t)L.npad);
-        const size_t zwords = (size_t)v.K * (kLvlBins + 2 * (size_t)kLvlCount);
+        const size_t head = 2 * 16 + 4;  // cost (K <= 15 x 8 bytes, 8-byte aligned at the block start), list_count
+        const size_t zwords = head + (size_t)v.K * (kLvlBins + 2 * (size_t)kLvlCount);
         v.zero0 = c.take<uint32_t>(zwords);
         v.zero_bytes = zwords * sizeof(uint32_t);
-        v.hist1 = v.zero0;
+        v.cost = reinterpret_cast<unsigned long long *>(v.zero0);
+        v.list_count = v.zero0 + 32;
+        v.hist1 = v.zero0 + head;
         v.cnt = v.hist1 + (size_t)v.K * kLvlBins;
         v.kmax = v.cnt + (size_t)v.K * kLvlCount;
         v.kmin = c.take<uint32_t>((size_t)v.K * kLvlCount);
@@ -158,6 +161,8 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         v.start = c.take<uint32_t>((size_t)v.K * (kLvlCount + 1));
         v.cursor = c.take<uint32_t>((size_t)v.K * kLvlCount);
         v.items = c.take<int2>((size_t)v.K * (size_t)L.npad);
+        v.list_cap = (uint32_t)((size_t)v.K * (size_t)L.npad);
+        v.list = c.take<unsigned long long>(v.list_cap);
     }
     // Only the triangle of the presorted matrix is ever written or read.  Storing just that (TriRows) halves
     // the workspace, but measured on the B200 it costs time: the build kernel's stores are 8-10 % slower with
@@ -411,13 +416,19 @@ static int run_level_build_w(const NdsLayout &L, int64_t n, int m, cudaStream_t 
     EVOXB_LAUNCH_CHECK("level_plan_kernel");
     level_assign_kernel<W><<<pos_blocks, 256, 0, s>>>(L.xt, npad, nn, v.K, v.bins, v.q, v.cnt, v.kmin, v.kmax);
     EVOXB_LAUNCH_CHECK("level_assign_kernel");
-    level_scan_kernel<<<(unsigned)v.K, 1024, 0, s>>>(v.cnt, v.kmin, v.kmax, v.start, v.cursor, nn, fallback);
+    level_scan_kernel<<<dim3(kLvlScanParts, (unsigned)v.K), 256, 0, s>>>(v.cnt, v.kmin, v.kmax, v.start, v.cursor, nn, v.cost,
+                                                                       fallback);
     EVOXB_LAUNCH_CHECK("level_scan_kernel");
     level_scatter_kernel<<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, v.q, npad, nn, v.kmin, v.kmax, v.cursor, v.items,
                                                                        fallback);
     EVOXB_LAUNCH_CHECK("level_scatter_kernel");
 
     const TriRows rows = make_rows(L);
+    if (cm && cm->nlocal <= 0) return 0;
+    level_fixup_find_kernel<W><<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(
+        L.xt, v.q, npad, nn, v.kmin, v.kmax, v.start, v.items, L.uid_row, L.uid_col, rows, cm ? *cm : ChunkMap{0, 1, L.nchunks},
+        v.list, v.list_count, v.list_cap, fallback);
+    EVOXB_LAUNCH_CHECK("level_fixup_find_kernel");
     TriGrid g = make_tri_grid(L.npad, n);
     if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
     constexpr int kRowTiles = LvlCfg<W>::kRowTiles;
@@ -443,10 +454,8 @@ static int run_level_build_w(const NdsLayout &L, int64_t n, int m, cudaStream_t 
     if (int rc = launch_dominance_build_tri_fallback(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D,
                                                      rows, g, gx, gy, fallback, s))
         return rc;
-    level_fixup_kernel<W><<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, v.q, npad, nn, v.kmin, v.kmax, v.start, v.items,
-                                                                        L.uid_row, L.uid_col, L.D, rows,
-                                                                        cm ? *cm : ChunkMap{0, 1, L.nchunks}, fallback);
-    EVOXB_LAUNCH_CHECK("level_fixup_kernel");
+    level_fixup_apply_kernel<<<296, 256, 0, s>>>(v.list, v.list_count, v.list_cap, L.D, fallback);
+    EVOXB_LAUNCH_CHECK("level_fixup_apply_kernel");
     return 0;
 }
 

@@ -30,8 +30,12 @@ constexpr int kLvlBudgetPerRow = 64;             // sum over mixed levels of row
 struct LevelBufs {
     int K, W;           // compared objectives (m - 1) and packed words per row
     uint32_t *q;        // [W][npad] level words, row form (guard bits clear); objective 2w+1 low half, 2w+2 high half
-    uint32_t *zero0;    // start of the region cleared before every call: hist1, cnt, kmax
+    uint32_t *zero0;    // start of the region cleared before every call: cost, list_count, hist1, cnt, kmax
     size_t zero_bytes;
+    unsigned long long *cost;  // [K] sum over mixed levels of rows^2
+    uint32_t *list_count;      // entries of list
+    unsigned long long *list;  // [list_cap] bits to clear after the build: (word index << 5) | bit
+    uint32_t list_cap;
     uint32_t *hist1;    // [K][kLvlBins]
     uint32_t *cnt;      // [K][kLvlCount] rows per level
     uint32_t *kmax;     // [K][kLvlCount] largest key of the level
@@ -149,72 +153,85 @@ level_assign_kernel(const float *__restrict__ xt, int npad, int n, int K, const 
 }
 
 // First slot of every level (exclusive scan of the rows per level), and the decision whether the fix-up is
-// affordable.  One CTA of 1024 threads per objective; the 32768 levels go through shared memory in four pieces of
-// 8192 so that every global access is coalesced (thread t owns 8 consecutive levels of a piece for the scan).
-constexpr int kLvlPiece = 8192;
-__global__ void __launch_bounds__(1024)
+// affordable.  grid = (kLvlScanParts, K), 256 threads: a CTA scans one quarter of an objective's levels; instead of
+// waiting for the quarters in front of it, it sums them itself (at most 96 KB of coalesced reads).  A warp owns
+// 1024 consecutive levels, lane l the levels l, l + 32, ... of them, so every access is coalesced and the scan is
+// 32 warp scans with a running carry.
+constexpr int kLvlScanParts = 4;
+__global__ void __launch_bounds__(256)
 level_scan_kernel(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ kmin, const uint32_t *__restrict__ kmax,
-                  uint32_t *__restrict__ start, uint32_t *__restrict__ cursor, int n, int *__restrict__ fallback) {
-    __shared__ uint32_t sh[kLvlPiece];
-    __shared__ uint32_t sh_warp[33];
-    __shared__ unsigned long long sh_cost;
-    __shared__ uint32_t sh_big;
-    const int k = blockIdx.x, t = threadIdx.x;
-    if (t == 0) {
-        sh_cost = 0ull;
-        sh_big = 0u;
+                  uint32_t *__restrict__ start, uint32_t *__restrict__ cursor, int n, unsigned long long *__restrict__ cost_acc,
+                  int *__restrict__ fallback) {
+    __shared__ uint32_t sh_warp[8];
+    __shared__ uint32_t sh_front[8];
+    const int k = blockIdx.y, part = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int kPart = kLvlCount / kLvlScanParts;  // 8192 levels = 8 warps x 1024
+    const uint32_t *ck = cnt + (size_t)k * kLvlCount;
+    // rows in the quarters in front of this one
+    uint32_t front = 0;
+    {
+        const uint4 *c4 = reinterpret_cast<const uint4 *>(ck);  // 16-byte aligned: kLvlCount * 4 bytes per objective
+#pragma unroll 8
+        for (int i = threadIdx.x; i < part * kPart / 4; i += 256) {
+            const uint4 v = c4[i];
+            front += v.x + v.y + v.z + v.w;
+        }
     }
-    uint32_t big = 0, carry = 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) front += __shfl_xor_sync(0xffffffffu, front, o);
+    if (lane == 0) sh_front[warp] = front;
+
+    const int l0 = part * kPart + warp * 1024;
+    uint32_t c[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) c[j] = ck[l0 + j * 32 + lane];
+    uint32_t big = 0;
     unsigned long long cost = 0;
-    for (int piece = 0; piece < kLvlCount / kLvlPiece; ++piece) {
-        const int i0 = k * kLvlCount + piece * kLvlPiece;
 #pragma unroll
-        for (int j = 0; j < kLvlPiece / 1024; ++j) {
-            const int i = i0 + j * 1024 + t;
-            const uint32_t c = cnt[i];
-            sh[j * 1024 + t] = c;
-            if (c > 1 && kmin[i] != kmax[i]) {
-                cost += (unsigned long long)c * c;
-                big = max(big, c);
-            }
+    for (int j = 0; j < 32; ++j) {
+        const int i = k * kLvlCount + l0 + j * 32 + lane;
+        if (c[j] > 1 && kmin[i] != kmax[i]) {
+            cost += (unsigned long long)c[j] * c[j];
+            big = max(big, c[j]);
         }
-        __syncthreads();
-        uint32_t v[8], mine = 0;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            v[e] = sh[t * 8 + e];
-            mine += v[e];
-        }
-        uint32_t total;
-        uint32_t base = carry + block_scan_1024(mine, sh_warp, &total);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            sh[t * 8 + e] = base;
-            base += v[e];
-        }
-        carry += total;
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < kLvlPiece / 1024; ++j) {
-            const uint32_t st = sh[j * 1024 + t];
-            start[k * (kLvlCount + 1) + piece * kLvlPiece + j * 1024 + t] = st;
-            cursor[i0 + j * 1024 + t] = st;
-        }
-        __syncthreads();
     }
-    if (t == 0) start[k * (kLvlCount + 1) + kLvlCount] = carry;
+    uint32_t carry = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        uint32_t incl = c[j];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+        c[j] = carry + incl - c[j];  // exclusive prefix inside the warp's 1024 levels
+        carry += tot;
+    }
+    if (lane == 0) sh_warp[warp] = carry;
+    __syncthreads();
+    uint32_t base = 0;
+    for (int w = 0; w < 8; ++w) {
+        base += sh_front[w];
+        if (w < warp) base += sh_warp[w];
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const uint32_t st = base + c[j];
+        start[k * (kLvlCount + 1) + l0 + j * 32 + lane] = st;
+        cursor[k * kLvlCount + l0 + j * 32 + lane] = st;
+    }
+    if (part == kLvlScanParts - 1 && threadIdx.x == 255) start[k * (kLvlCount + 1) + kLvlCount] = base + carry;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         cost += __shfl_xor_sync(0xffffffffu, cost, o);
         big = max(big, __shfl_xor_sync(0xffffffffu, big, o));
     }
-    if ((t & 31) == 0) {
-        if (cost) atomicAdd(&sh_cost, cost);
-        if (big) atomicMax(&sh_big, big);
+    if (lane == 0) {
+        bool over = big > kLvlMaxBucket;
+        if (cost) over = over || atomicAdd(&cost_acc[k], cost) + cost > (unsigned long long)kLvlBudgetPerRow * (unsigned long long)n;
+        if (over) atomicExch(fallback, 1);
     }
-    __syncthreads();
-    if (t == 0 && (sh_cost > (unsigned long long)kLvlBudgetPerRow * (unsigned long long)n || sh_big > kLvlMaxBucket))
-        atomicExch(fallback, 1);
 }
 
 __device__ __forceinline__ uint32_t level_field(const uint32_t *__restrict__ q, int npad, int k, int p) {
@@ -236,46 +253,94 @@ level_scatter_kernel(const float *__restrict__ xt, const uint32_t *__restrict__ 
     items[(int64_t)k * npad + atomicAdd(&cursor[i], 1u)] = make_int2(p, __float_as_int(x));
 }
 
-// Clears the bits of the pairs (row i, column j in i's chunk or a later one) that share a level in objective k + 1
-// but have x_ik > x_jk.  Only bits that the level kernel can have set are touched (all other levels <=, uid test),
-// so the atomics stay few.  grid = (npad / 256, K); one thread per (position, objective) walks its level, four
-// members per round so that their loads are in flight together.
+// Finds the pairs (row i, column j in i's chunk or a later one) that share a level in objective k + 1 but have
+// x_ik > x_jk, and whose bit the level kernel will set (all other levels <=, uid test): their bits must be cleared.
+// Runs BEFORE the build kernel, while levels and items are still in the L2 (the build's 3 GB of stores evict
+// them), and only records (word index << 5 | bit); level_fixup_apply_kernel clears them after the build.
+// grid = (npad / 256, K); one thread per (position, objective) walks its level, four members per round so that
+// their loads are in flight together.  A full list raises the fall-back flag (the build has not started yet).
+constexpr int kLvlFindBuf = 1024;  // entries a CTA collects in shared memory before it reserves room in the list
 template <int W>
 __global__ void __launch_bounds__(256)
-level_fixup_kernel(const float *__restrict__ xt, const uint32_t *__restrict__ q, int npad, int n,
-                   const uint32_t *__restrict__ kmin, const uint32_t *__restrict__ kmax, const uint32_t *__restrict__ start,
-                   const int2 *__restrict__ items, const int *__restrict__ uid_row, const int *__restrict__ uid_col,
-                   uint32_t *__restrict__ D, TriRows rows, ChunkMap cm, const int *__restrict__ fallback) {
+level_fixup_find_kernel(const float *__restrict__ xt, const uint32_t *__restrict__ q, int npad, int n,
+                        const uint32_t *__restrict__ kmin, const uint32_t *__restrict__ kmax,
+                        const uint32_t *__restrict__ start, const int2 *__restrict__ items, const int *__restrict__ uid_row,
+                        const int *__restrict__ uid_col, TriRows rows, ChunkMap cm, unsigned long long *__restrict__ list,
+                        uint32_t *__restrict__ list_count, uint32_t list_cap, int *__restrict__ fallback) {
+    __shared__ unsigned long long sh_list[kLvlFindBuf];
+    __shared__ uint32_t sh_count, sh_base;
     if (*fallback) return;
+    if (threadIdx.x == 0) sh_count = 0u;
+    __syncthreads();
     const int pi = blockIdx.x * 256 + threadIdx.x, k = blockIdx.y;
-    if (pi >= n) return;
-    const float xi = xt[(int64_t)(k + 1) * npad + pi];
-    if (xi != xi) return;
-    const int lv = (int)level_field(q, npad, k, pi);
-    const int i = k * kLvlCount + lv;
-    if (kmin[i] == kmax[i]) return;
-    const uint32_t s0 = start[k * (kLvlCount + 1) + lv], s1 = start[k * (kLvlCount + 1) + lv + 1];
-    const int2 *it = items + (int64_t)k * npad;
-    const int ci = pi >> 12;
-    for (uint32_t t0 = s0; t0 < s1; t0 += 4) {
-        int2 mem[4];
+    bool active = pi < n;
+    float xi = 0.0f;
+    int lv = 0;
+    if (active) {
+        xi = xt[(int64_t)(k + 1) * npad + pi];
+        active = xi == xi;
+    }
+    if (active) {
+        lv = (int)level_field(q, npad, k, pi);
+        const int i = k * kLvlCount + lv;
+        active = kmin[i] != kmax[i];
+    }
+    if (active) {
+        const uint32_t s0 = start[k * (kLvlCount + 1) + lv], s1 = start[k * (kLvlCount + 1) + lv + 1];
+        const int2 *it = items + (int64_t)k * npad;
+        const int ci = pi >> 12;
+        for (uint32_t t0 = s0; t0 < s1; t0 += 4) {
+            int2 mem[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) mem[e] = (t0 + e < s1) ? __ldg(it + t0 + e) : make_int2(pi, 0);
+            for (int e = 0; e < 4; ++e) mem[e] = (t0 + e < s1) ? __ldg(it + t0 + e) : make_int2(pi, 0);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int pj = mem[e].x;
-            // i is the row: j must sit in the same chunk (where positions carry no order) or in a later one
-            if (pj == pi || (pj >> 12) < ci) continue;
-            if (!(xi > __int_as_float(mem[e].y))) continue;  // floats agree with the levels: nothing to clear
-            const int off = (pj >> 12) - cm.first;
-            if (off < 0 || off % cm.stride != 0) continue;    // column chunk of another GPU
-            uint32_t d = kLvlGuard;
+            for (int e = 0; e < 4; ++e) {
+                const int pj = mem[e].x;
+                // i is the row: j must sit in the same chunk (where positions carry no order) or in a later one
+                if (pj == pi || (pj >> 12) < ci) continue;
+                if (!(xi > __int_as_float(mem[e].y))) continue;  // floats agree with the levels: nothing to clear
+                const int off = (pj >> 12) - cm.first;
+                if (off < 0 || off % cm.stride != 0) continue;    // column chunk of another GPU
+                uint32_t d = kLvlGuard;
 #pragma unroll
-            for (int w = 0; w < W; ++w) d &= (q[(int64_t)w * npad + pj] | kLvlGuard) - q[(int64_t)w * npad + pi];
-            if (d != kLvlGuard || !(uid_row[pi] < uid_col[pj])) continue;  // the level kernel left this bit clear
-            const int64_t row_word0 = rows.tri ? rows.vstart(pi) * 4 : (int64_t)pi * rows.row_words;
-            atomicAnd(D + row_word0 + (int64_t)(off / cm.stride) * kChunkWords + ((pj & 4095) >> 5), ~(1u << (pj & 31)));
+                for (int w = 0; w < W; ++w) d &= (q[(int64_t)w * npad + pj] | kLvlGuard) - q[(int64_t)w * npad + pi];
+                if (d != kLvlGuard || !(uid_row[pi] < uid_col[pj])) continue;  // the level kernel leaves this bit clear
+                const int64_t row_word0 = rows.tri ? rows.vstart(pi) * 4 : (int64_t)pi * rows.row_words;
+                const unsigned long long word =
+                    (unsigned long long)(row_word0 + (int64_t)(off / cm.stride) * kChunkWords + ((pj & 4095) >> 5));
+                const unsigned long long entry = (word << 5) | (unsigned long long)(pj & 31);
+                const uint32_t mine = atomicAdd(&sh_count, 1u);
+                if (mine < kLvlFindBuf) {
+                    sh_list[mine] = entry;
+                } else {  // rare: the CTA's buffer is full
+                    const uint32_t slot = atomicAdd(list_count, 1u);
+                    if (slot < list_cap) list[slot] = entry;
+                    else atomicExch(fallback, 1);
+                }
+            }
         }
+    }
+    __syncthreads();
+    const uint32_t held = min(sh_count, (uint32_t)kLvlFindBuf);
+    if (threadIdx.x == 0 && held) sh_base = atomicAdd(list_count, held);
+    __syncthreads();
+    if (held) {
+        if (sh_base + held > list_cap) {
+            if (threadIdx.x == 0) atomicExch(fallback, 1);
+        } else {
+            for (uint32_t i = threadIdx.x; i < held; i += 256) list[sh_base + i] = sh_list[i];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+level_fixup_apply_kernel(const unsigned long long *__restrict__ list, const uint32_t *__restrict__ list_count, uint32_t list_cap,
+                         uint32_t *__restrict__ D, const int *__restrict__ fallback) {
+    if (*fallback) return;
+    const uint32_t count = min(*list_count, list_cap);
+    for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < count; i += gridDim.x * 256) {
+        const unsigned long long e = list[i];
+        atomicAnd(D + (e >> 5), ~(1u << (uint32_t)(e & 31ull)));
     }
 }
 

@@ -29,6 +29,7 @@ PATH_ENV = {
     "grid_peer": {"EVOXB_PEEL_MODE": "grid"},      # peel_p2p_kernel
     "nccl_allgather": {"EVOXB_NO_P2P": "1"},       # one ncclAllGather per front
     "auto": {},                                    # whatever the library picks
+    "levels": {"EVOXB_BUILD_MODE": "levels"},      # matrix built from 15-bit levels at every size (csrc/levels.cuh)
 }
 
 
@@ -100,12 +101,12 @@ def _run(world, path="auto", cases=CASES):
             assert not why, f"rank {r} of {world} ({path}): {kind} {n}x{m}: {why}"
 
 
-@pytest.mark.parametrize("path", ["data_flow", "grid_peer", "nccl_allgather", "auto"])
+@pytest.mark.parametrize("path", ["data_flow", "grid_peer", "nccl_allgather", "auto", "levels"])
 def test_sharded_world_size_1(path):
     _run(1, path)
 
 
-@pytest.mark.parametrize("path", ["data_flow", "grid_peer", "nccl_allgather", "auto"])
+@pytest.mark.parametrize("path", ["data_flow", "grid_peer", "nccl_allgather", "auto", "levels"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_sharded_multi_gpu(world, path):
     if torch.cuda.device_count() < world:
