@@ -352,25 +352,28 @@ inline int launch_dominance_build_tri_fallback(const float *xt, int64_t npad, in
 // exactly as in the float kernel.
 constexpr uint32_t kLvlGuard = 0x80008000u;
 
-// bad = some guard bit of (t & dl) is missing; returns the ballot of the pairs that pass
-__device__ __forceinline__ uint32_t lvl_ballot(uint32_t t, uint32_t dl) {
+// bad = some guard bit of (t & dl) is missing; returns the ballot of the pairs that pass and adds this lane's
+// pair to cnt (the lane's column gains a dominator)
+__device__ __forceinline__ uint32_t lvl_ballot(uint32_t t, uint32_t dl, uint32_t &cnt) {
     uint32_t b, dummy;
     asm("{ .reg .pred p, q;\n"
         "setp.eq.u32 q, 0, 0;\n"
-        "lop3.and.b32 %1|p, %2, %3, 0x80008000, 0x2a, q;\n"
+        "lop3.and.b32 %1|p, %3, %4, 0x80008000, 0x2a, q;\n"
+        "@!p add.u32 %2, %2, 1;\n"
         "vote.sync.ballot.b32 %0, !p, 0xffffffff; }"
-        : "=r"(b), "=r"(dummy)
+        : "=r"(b), "=r"(dummy), "+r"(cnt)
         : "r"(t), "r"(dl));
     return b;
 }
-__device__ __forceinline__ uint32_t lvl_ballot_uid(uint32_t t, uint32_t dl, int ui, int uj) {
+__device__ __forceinline__ uint32_t lvl_ballot_uid(uint32_t t, uint32_t dl, int ui, int uj, uint32_t &cnt) {
     uint32_t b, dummy;
     asm("{ .reg .pred p, q, r;\n"
         "setp.eq.u32 q, 0, 0;\n"
-        "lop3.and.b32 %1|p, %2, %3, 0x80008000, 0x2a, q;\n"
-        "setp.lt.and.s32 r, %4, %5, !p;\n"
+        "lop3.and.b32 %1|p, %3, %4, 0x80008000, 0x2a, q;\n"
+        "setp.lt.and.s32 r, %5, %6, !p;\n"
+        "@r add.u32 %2, %2, 1;\n"
         "vote.sync.ballot.b32 %0, r, 0xffffffff; }"
-        : "=r"(b), "=r"(dummy)
+        : "=r"(b), "=r"(dummy), "+r"(cnt)
         : "r"(t), "r"(dl), "r"(ui), "r"(uj));
     return b;
 }
@@ -407,7 +410,7 @@ __global__ void __launch_bounds__(kBuildThreads)
 dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t n_rows, const int *__restrict__ uid_row,
                            const int *__restrict__ uid_col, const float *__restrict__ tile_min1,
                            const float *__restrict__ tile_max1, uint32_t *__restrict__ D, TriRows rows, TriGrid g,
-                           const int *__restrict__ fallback) {
+                           int *__restrict__ count, const int *__restrict__ fallback) {
     using Cfg = LvlCfg<W>;
     constexpr int WP = Cfg::kPad, R = Cfg::kRows, NB = Cfg::kBlocks;
     __shared__ __align__(16) uint32_t qs[R][WP];          // row level words
@@ -417,6 +420,8 @@ dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t
     __shared__ __align__(16) uint32_t stage[kBuildThreads / 32][32][kC];
     __shared__ int rb_min2[NB], rb_max2[NB], rb_umax[NB];  // per 32-row block: band of objective 2's level, largest uid
     __shared__ int oc_min2[8], oc_max2[8], oc_umin[8];     // per 128 columns
+    constexpr bool kSmemCnt = W <= 7;                      // W = 8 has no shared memory left: counts go straight to global
+    __shared__ int ccnt[kSmemCnt ? kTileCols : 1];         // dominators found by this CTA, per column
     __shared__ int next_item;
     if (*fallback) return;  // the levels are too coarse for this population: the float kernel runs instead
     const int lane = threadIdx.x & 31;
@@ -463,7 +468,10 @@ dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t
         const int w = t / kTileCols, j = t - w * kTileCols;
         qc[w][j] = q[(int64_t)w * npad + col0 + j] | kLvlGuard;
     }
-    for (int j = threadIdx.x; j < kTileCols; j += kBuildThreads) uc[j] = uid_col[col0 + j];
+    for (int j = threadIdx.x; j < kTileCols; j += kBuildThreads) {
+        uc[j] = uid_col[col0 + j];
+        if (kSmemCnt) ccnt[j] = 0;
+    }
     if (threadIdx.x == 0) next_item = 0;
     __syncthreads();
     // bands: warp w reduces row blocks w, w + 8, ... and the columns of octile w.  The band of objective 2 is the
@@ -527,7 +535,7 @@ dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t
                 uint32_t t = xj[c][F] - a[F];                                                               \
                 _Pragma("unroll") for (int w = F + 1; w < W - 1; ++w) t &= xj[c][w] - a[w];                 \
                 const uint32_t dl = (W - 1 > F) ? xj[c][W - 1] - a[W - 1] : t;                              \
-                b[c] = WITH_UID ? lvl_ballot_uid(t, dl, ui, uj[c]) : lvl_ballot(t, dl);                     \
+                b[c] = WITH_UID ? lvl_ballot_uid(t, dl, ui, uj[c], cn[c]) : lvl_ballot(t, dl, cn[c]);       \
             }                                                                                               \
             if (lane == 0) *reinterpret_cast<uint4 *>(st[ii]) = make_uint4(b[0], b[1], b[2], b[3]);         \
         }                                                                                                   \
@@ -559,8 +567,10 @@ dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t
             const bool dead = rb_min2[blk] > c_max2;    // no pair of the block passes objective 2
             const bool sure2 = rb_max2[blk] <= c_min2;  // every pair passes it
             if (!dead) {
+                uint32_t cn[kC];
 #pragma unroll
                 for (int c = 0; c < kC; ++c) {
+                    cn[c] = 0u;
                     uj[c] = uc[oct * 128 + c * 32 + lane];
 #pragma unroll
                     for (int w = 0; w < W; ++w) xj[c][w] = qc[w][oct * 128 + c * 32 + lane];
@@ -572,6 +582,13 @@ dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t
                 } else {
                     EVOXB_LVL_BLOCK(false, 0)
                 }
+                // K2 for free: the lane has counted the rows of the block that dominate each of its 4 columns
+#pragma unroll
+                for (int c = 0; c < kC; ++c)
+                    if (cn[c]) {
+                        if (kSmemCnt) atomicAdd(&ccnt[oct * 128 + c * 32 + lane], (int)cn[c]);
+                        else atomicAdd(count + col0 + oct * 128 + c * 32 + lane, (int)cn[c]);
+                    }
             }
             if (h == 0) out0 = v; else out1 = v;
         }
@@ -584,6 +601,11 @@ dominance_build_lvl_kernel(const uint32_t *__restrict__ q, int64_t npad, int64_t
         }
     }
 #undef EVOXB_LVL_BLOCK
+    if (kSmemCnt) {
+        __syncthreads();
+        for (int j = threadIdx.x; j < kTileCols; j += kBuildThreads)
+            if (ccnt[j]) atomicAdd(count + col0 + j, ccnt[j]);
+    }
 }
 
 // ---- a2: dense boolean relation between two different sets (utils/common.py:101-104) ----------

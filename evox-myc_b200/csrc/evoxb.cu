@@ -163,6 +163,7 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         v.items = c.take<int2>((size_t)v.K * (size_t)L.npad);
         v.list_cap = (uint32_t)((size_t)v.K * (size_t)L.npad);
         v.list = c.take<unsigned long long>(v.list_cap);
+        v.list_col = c.take<int>(v.list_cap);
     }
     // Only the triangle of the presorted matrix is ever written or read.  Storing just that (TriRows) halves
     // the workspace, but measured on the B200 it costs time: the build kernel's stores are 8-10 % slower with
@@ -426,8 +427,9 @@ static int run_level_build_w(const NdsLayout &L, int64_t n, int m, cudaStream_t 
     const TriRows rows = make_rows(L);
     if (cm && cm->nlocal <= 0) return 0;
     level_fixup_find_kernel<W><<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(
-        L.xt, v.q, npad, nn, v.kmin, v.kmax, v.start, v.items, L.uid_row, L.uid_col, rows, cm ? *cm : ChunkMap{0, 1, L.nchunks},
-        v.list, v.list_count, v.list_cap, fallback);
+        L.xt, v.q, npad, nn, v.kmin, v.kmax, v.start, v.items, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, rows,
+        cm ? *cm : ChunkMap{0, 1, L.nchunks},
+        v.list, v.list_col, v.list_count, v.list_cap, fallback);
     EVOXB_LAUNCH_CHECK("level_fixup_find_kernel");
     TriGrid g = make_tri_grid(L.npad, n);
     if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
@@ -446,15 +448,15 @@ static int run_level_build_w(const NdsLayout &L, int64_t n, int m, cudaStream_t 
     }
     if (rows.tri)
         dominance_build_lvl_kernel<W, true><<<grid, kBuildThreads, 0, s>>>(v.q, L.npad, n, L.uid_row, L.uid_col, L.tile_min1,
-                                                                          L.tile_max1, L.D, rows, g, fallback);
+                                                                          L.tile_max1, L.D, rows, g, L.count, fallback);
     else
         dominance_build_lvl_kernel<W, false><<<grid, kBuildThreads, 0, s>>>(v.q, L.npad, n, L.uid_row, L.uid_col, L.tile_min1,
-                                                                           L.tile_max1, L.D, rows, g, fallback);
+                                                                           L.tile_max1, L.D, rows, g, L.count, fallback);
     EVOXB_LAUNCH_CHECK("dominance_build_lvl_kernel");
     if (int rc = launch_dominance_build_tri_fallback(L.xt, L.npad, n, m, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, L.D,
                                                      rows, g, gx, gy, fallback, s))
         return rc;
-    level_fixup_apply_kernel<<<296, 256, 0, s>>>(v.list, v.list_count, v.list_cap, L.D, fallback);
+    level_fixup_apply_kernel<<<296, 256, 0, s>>>(v.list, v.list_col, v.list_count, v.list_cap, L.D, L.count, fallback);
     EVOXB_LAUNCH_CHECK("level_fixup_apply_kernel");
     return 0;
 }
@@ -512,8 +514,9 @@ static int run_nds(const float *fitness, int64_t n, int m, int32_t *rank, const 
 
     prof.mark("dominator_count", s);
     const TileBands tb{L.tri ? L.tile_min1 : nullptr, L.tri ? L.tile_max1 : nullptr};
+    // with the level build the counts are already there; the kernel then only runs if that build fell back
     dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, make_rows(L), L.nchunks, n, tri, ChunkMap{0, 1, L.nchunks},
-                                                           L.count, tb);
+                                                           L.count, tb, L.levels ? &L.ctrl->level_fallback : nullptr);
     EVOXB_LAUNCH_CHECK("dominator_count_kernel");
 
     prof.mark("peel", s);
@@ -643,7 +646,8 @@ static int run_nds_sharded(const float *fitness, int64_t n, int m, int32_t *rank
     const TileBands tb{L.tile_min1, L.tile_max1};
     prof.mark("dominator_count", s);
     if (L.cm.nlocal > 0) {
-        dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, make_rows(L), L.nchunks, n, 1, L.cm, L.count, tb);
+        dominator_count_kernel<<<blocks, kPeelThreads, 0, s>>>(L.D, make_rows(L), L.nchunks, n, 1, L.cm, L.count, tb,
+                                                               L.levels ? &L.ctrl->level_fallback : nullptr);
         EVOXB_LAUNCH_CHECK("dominator_count_kernel");
     }
 

@@ -35,6 +35,7 @@ struct LevelBufs {
     unsigned long long *cost;  // [K] sum over mixed levels of rows^2
     uint32_t *list_count;      // entries of list
     unsigned long long *list;  // [list_cap] bits to clear after the build: (word index << 5) | bit
+    int *list_col;             // [list_cap] column position of the entry (its dominator count drops with the bit)
     uint32_t list_cap;
     uint32_t *hist1;    // [K][kLvlBins]
     uint32_t *cnt;      // [K][kLvlCount] rows per level
@@ -265,9 +266,12 @@ __global__ void __launch_bounds__(256)
 level_fixup_find_kernel(const float *__restrict__ xt, const uint32_t *__restrict__ q, int npad, int n,
                         const uint32_t *__restrict__ kmin, const uint32_t *__restrict__ kmax,
                         const uint32_t *__restrict__ start, const int2 *__restrict__ items, const int *__restrict__ uid_row,
-                        const int *__restrict__ uid_col, TriRows rows, ChunkMap cm, unsigned long long *__restrict__ list,
+                        const int *__restrict__ uid_col, const float *__restrict__ tile_min1,
+                        const float *__restrict__ tile_max1, TriRows rows, ChunkMap cm,
+                        unsigned long long *__restrict__ list, int *__restrict__ list_col,
                         uint32_t *__restrict__ list_count, uint32_t list_cap, int *__restrict__ fallback) {
     __shared__ unsigned long long sh_list[kLvlFindBuf];
+    __shared__ int sh_col[kLvlFindBuf];
     __shared__ uint32_t sh_count, sh_base;
     if (*fallback) return;
     if (threadIdx.x == 0) sh_count = 0u;
@@ -289,6 +293,7 @@ level_fixup_find_kernel(const float *__restrict__ xt, const uint32_t *__restrict
         const uint32_t s0 = start[k * (kLvlCount + 1) + lv], s1 = start[k * (kLvlCount + 1) + lv + 1];
         const int2 *it = items + (int64_t)k * npad;
         const int ci = pi >> 12;
+        const float r_lo = tile_min1[pi >> 10];
         for (uint32_t t0 = s0; t0 < s1; t0 += 4) {
             int2 mem[4];
 #pragma unroll
@@ -305,6 +310,9 @@ level_fixup_find_kernel(const float *__restrict__ xt, const uint32_t *__restrict
 #pragma unroll
                 for (int w = 0; w < W; ++w) d &= (q[(int64_t)w * npad + pj] | kLvlGuard) - q[(int64_t)w * npad + pi];
                 if (d != kLvlGuard || !(uid_row[pi] < uid_col[pj])) continue;  // the level kernel leaves this bit clear
+                // a tile pair that the build kernels skip on their x_1 test is never written: its words hold whatever
+                // the workspace held before, and must not be taken for bits that were set and counted
+                if (r_lo > tile_max1[pj >> 10]) continue;
                 const int64_t row_word0 = rows.tri ? rows.vstart(pi) * 4 : (int64_t)pi * rows.row_words;
                 const unsigned long long word =
                     (unsigned long long)(row_word0 + (int64_t)(off / cm.stride) * kChunkWords + ((pj & 4095) >> 5));
@@ -312,10 +320,15 @@ level_fixup_find_kernel(const float *__restrict__ xt, const uint32_t *__restrict
                 const uint32_t mine = atomicAdd(&sh_count, 1u);
                 if (mine < kLvlFindBuf) {
                     sh_list[mine] = entry;
+                    sh_col[mine] = pj;
                 } else {  // rare: the CTA's buffer is full
                     const uint32_t slot = atomicAdd(list_count, 1u);
-                    if (slot < list_cap) list[slot] = entry;
-                    else atomicExch(fallback, 1);
+                    if (slot < list_cap) {
+                        list[slot] = entry;
+                        list_col[slot] = pj;
+                    } else {
+                        atomicExch(fallback, 1);
+                    }
                 }
             }
         }
@@ -328,19 +341,26 @@ level_fixup_find_kernel(const float *__restrict__ xt, const uint32_t *__restrict
         if (sh_base + held > list_cap) {
             if (threadIdx.x == 0) atomicExch(fallback, 1);
         } else {
-            for (uint32_t i = threadIdx.x; i < held; i += 256) list[sh_base + i] = sh_list[i];
+            for (uint32_t i = threadIdx.x; i < held; i += 256) {
+                list[sh_base + i] = sh_list[i];
+                list_col[sh_base + i] = sh_col[i];
+            }
         }
     }
 }
 
+// Clears the recorded bits; a bit that was set takes one dominator off its column's count (the level kernel
+// counted it).  A pair recorded twice (two objectives the wrong way round) is only counted down once.
 __global__ void __launch_bounds__(256)
-level_fixup_apply_kernel(const unsigned long long *__restrict__ list, const uint32_t *__restrict__ list_count, uint32_t list_cap,
-                         uint32_t *__restrict__ D, const int *__restrict__ fallback) {
+level_fixup_apply_kernel(const unsigned long long *__restrict__ list, const int *__restrict__ list_col,
+                         const uint32_t *__restrict__ list_count, uint32_t list_cap, uint32_t *__restrict__ D,
+                         int *__restrict__ count, const int *__restrict__ fallback) {
     if (*fallback) return;
-    const uint32_t count = min(*list_count, list_cap);
-    for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < count; i += gridDim.x * 256) {
+    const uint32_t n_entries = min(*list_count, list_cap);
+    for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < n_entries; i += gridDim.x * 256) {
         const unsigned long long e = list[i];
-        atomicAnd(D + (e >> 5), ~(1u << (uint32_t)(e & 31ull)));
+        const uint32_t bit = 1u << (uint32_t)(e & 31ull);
+        if (atomicAnd(D + (e >> 5), ~bit) & bit) atomicSub(count + list_col[i], 1);
     }
 }
 

@@ -338,9 +338,12 @@ __device__ void accumulate_front(const uint32_t *__restrict__ D, TriRows rows, i
 // K2: count[j] += number of rows in [0, n_rows) that dominate j   (non_dominate.py:61)
 __global__ void __launch_bounds__(kPeelThreads)
 dominator_count_kernel(const uint32_t *__restrict__ D, TriRows rows, int nchunks, int64_t n_rows, int tri,
-                       ChunkMap cm, int *__restrict__ count, TileBands tb) {
+                       ChunkMap cm, int *__restrict__ count, TileBands tb, const int *__restrict__ go) {
     __shared__ PeelSmem sm;
     __shared__ PrefixSmem ps;
+    // go != nullptr: the level build has already counted the dominators while it built the matrix (levels.cuh);
+    // this pass only runs when that build was abandoned on the device for the float kernel
+    if (go && *go == 0) return;
     build_prefix(nullptr, nchunks, n_rows, tri != 0, cm, ps);
     accumulate_front(D, rows, nchunks, tri != 0, cm, nullptr, ps, count, +1, sm, tb);
 }
