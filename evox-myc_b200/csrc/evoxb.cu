@@ -160,7 +160,8 @@ static NdsLayout nds_layout(void *ws, int64_t n, int m, int64_t n_rows, int nran
         v.bins = c.take<uint2>((size_t)v.K * kLvlBins);
         v.start = c.take<uint32_t>((size_t)v.K * (kLvlCount + 1));
         v.cursor = c.take<uint32_t>((size_t)v.K * kLvlCount);
-        v.items = c.take<int2>((size_t)v.K * (size_t)L.npad);
+        v.items4 = c.take<int4>((size_t)v.K * (size_t)L.npad * (v.W <= 2 ? 1 : 0) + (v.W <= 2 ? 0 : 1));
+        v.items = v.W <= 2 ? reinterpret_cast<int2 *>(v.items4) : c.take<int2>((size_t)v.K * (size_t)L.npad);
         v.list_cap = (uint32_t)((size_t)v.K * (size_t)L.npad);
         v.list = c.take<unsigned long long>(v.list_cap);
         v.list_col = c.take<int>(v.list_cap);
@@ -420,16 +421,28 @@ static int run_level_build_w(const NdsLayout &L, int64_t n, int m, cudaStream_t 
     level_scan_kernel<<<dim3(kLvlScanParts, (unsigned)v.K), 256, 0, s>>>(v.cnt, v.kmin, v.kmax, v.start, v.cursor, nn, v.cost,
                                                                        fallback);
     EVOXB_LAUNCH_CHECK("level_scan_kernel");
-    level_scatter_kernel<<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, v.q, npad, nn, v.kmin, v.kmax, v.cursor, v.items,
-                                                                       fallback);
-    EVOXB_LAUNCH_CHECK("level_scatter_kernel");
+    if (W <= 2) {
+        EVOXB_CUDA(cudaMemsetAsync(v.items4, 0xff, sizeof(int4) * (size_t)v.K * (size_t)L.npad, s));
+        level_scatter_packed_kernel<<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, v.q, npad, nn, W, v.kmin, v.kmax,
+                                                                                  v.cursor, v.items4, fallback);
+        EVOXB_LAUNCH_CHECK("level_scatter_packed_kernel");
+    } else {
+        level_scatter_kernel<<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(L.xt, v.q, npad, nn, v.kmin, v.kmax, v.cursor,
+                                                                           v.items, fallback);
+        EVOXB_LAUNCH_CHECK("level_scatter_kernel");
+    }
 
     const TriRows rows = make_rows(L);
     if (cm && cm->nlocal <= 0) return 0;
-    level_fixup_find_kernel<W><<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(
-        L.xt, v.q, npad, nn, v.kmin, v.kmax, v.start, v.items, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, rows,
-        cm ? *cm : ChunkMap{0, 1, L.nchunks},
-        v.list, v.list_col, v.list_count, v.list_cap, fallback);
+    if (W <= 2) {
+        level_fixup_find_packed_kernel<<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(
+            v.items4, npad, v.start, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, rows, cm ? *cm : ChunkMap{0, 1, L.nchunks},
+            v.list, v.list_col, v.list_count, v.list_cap, fallback);
+    } else {
+        level_fixup_find_kernel<W><<<dim3(pos_blocks, (unsigned)v.K), 256, 0, s>>>(
+            L.xt, v.q, npad, nn, v.kmin, v.kmax, v.start, v.items, L.uid_row, L.uid_col, L.tile_min1, L.tile_max1, rows,
+            cm ? *cm : ChunkMap{0, 1, L.nchunks}, v.list, v.list_col, v.list_count, v.list_cap, fallback);
+    }
     EVOXB_LAUNCH_CHECK("level_fixup_find_kernel");
     TriGrid g = make_tri_grid(L.npad, n);
     if (g.total > 0x7fffffffll) return fail(EVOXB_E_UNSUPPORTED, "too many tiles (%lld)", g.total);
