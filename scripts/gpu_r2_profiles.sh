@@ -16,7 +16,11 @@ for shape in 262144x5 65536x3; do
 done
 EVOXB_PEEL_MODE=grid python scripts/profile_step_sharded.py 262144x5 > $OUT/plain_c4_sharded.log 2>&1 && EVOXB_PEEL_MODE=grid ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 200 --csv --log-file $OUT/launches_c4sharded_N262144_M5_w1_${VER}.csv python scripts/profile_step_sharded.py 262144x5 > $OUT/ncu_c4_sharded.log 2>&1
 echo "{\"src_hash\": \"$HASH\", \"command\": \"EVOXB_PEEL_MODE=grid ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none python scripts/profile_step_sharded.py 262144x5\"}" > $OUT/launches_c4sharded_N262144_M5_w1_${VER}.csv.meta.json
-python scripts/profile_nsga3.py > /dev/null 2>&1 && ncu --set full --clock-control none --import-source on -k regex:'n3_associate|n3_niche' -s 2 -c 2 -o $OUT/prof_c5n3 -f python scripts/profile_nsga3.py > $OUT/ncu_c5n3_full.log 2>&1
+# full captures: gpurun brings back at most 64 MiB, a report with sources is 10 MB per kernel
 python scripts/profile_step.py 262144x5 > /dev/null 2>&1 && ncu --set full --clock-control none --import-source on -k regex:'dominance_build_lvl|peel_persistent|level_fixup_find' -s 3 -c 3 -o $OUT/prof_c4 -f python scripts/profile_step.py 262144x5 > $OUT/ncu_c4_full.log 2>&1
-python scripts/profile_step.py 65536x3 > /dev/null 2>&1 && ncu --set full --clock-control none --import-source on -k regex:'peel_flow|presort_coop' -s 2 -c 2 -o $OUT/prof_c2 -f python scripts/profile_step.py 65536x3 > $OUT/ncu_c2_full.log 2>&1
+if [ "${FULL:-0}" = "1" ]; then
+python scripts/profile_nsga3.py > /dev/null 2>&1 && ncu --set full --clock-control none -k regex:'n3_associate|n3_niche' -s 2 -c 2 -o $OUT/prof_c5n3 -f python scripts/profile_nsga3.py > $OUT/ncu_c5n3_full.log 2>&1
+python scripts/profile_step.py 65536x3 > /dev/null 2>&1 && ncu --set full --clock-control none -k regex:'peel_flow|presort_coop' -s 2 -c 2 -o $OUT/prof_c2 -f python scripts/profile_step.py 65536x3 > $OUT/ncu_c2_full.log 2>&1
+fi
+du -sh $OUT
 ls -la $OUT; tail -c 300 $OUT/bench.err
