@@ -462,6 +462,8 @@ def run_gpu_arm(args, n, m, desc):
                    "l2": "working set (bit-packed dominance matrix, N^2/8 bytes per step) exceeds the 126 MB L2"
                          if n * n / 8 / world > 126e6 else "L2 flushed by the matrix rewrite of each step",
                    "cores": host_cores(),
+                   "matrix_build": ("15-bit integer levels of the float objectives + exact fix-up (csrc/levels.cuh); ranks bit-exact "
+                                    "with the float compares" if build_uses_levels(n, m) else "float compares"),
                    "parallelism": "single GPU" if world == 1 else
                    f"dominance matrix sharded by column chunk over {world} GPUs; front bitmask (N/8 bytes per front) exchanged by: {exchange['path']}"},
         "e2e": {"value": pairs / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
