@@ -158,12 +158,13 @@ def cpu_sample_rows(n: int, m: int, budget_s: float) -> int:
     return ns
 
 
-def cpu_step(x: np.ndarray) -> float:
+def cpu_step(x: np.ndarray, want_result: bool = False):
     from oracle import c_oracle
 
     t0 = time.perf_counter()
-    c_oracle.nsga2_select(x, x.shape[0] // 2, nthreads=host_cores())
-    return time.perf_counter() - t0
+    res = c_oracle.nsga2_select(x, x.shape[0] // 2, nthreads=host_cores())
+    dt = time.perf_counter() - t0
+    return (dt, res) if want_result else dt
 
 
 def run_reference_arm(args, n, m, desc):
@@ -449,9 +450,19 @@ def run_gpu_arm(args, n, m, desc):
 
         ns = cpu_sample_rows(n, m, budget_s=20.0)
         xs = make_fitness(ns, m, 0)
-        dt = cpu_step(xs)
+        dt, (w_order, w_rank, w_crowd) = cpu_step(xs, want_result=True)
         cpu = {"value": ns * ns / dt, "unit": UNIT, "cores": host_cores(), "kind": "port",
                "sample": f"{ns} of {n} rows (same distribution, M={m}), one step = {dt:.2f} s"}
+        if not args.no_parity:
+            # the baseline's step doubles as the checker: same rows through the GPU path, outside every timed region
+            order_s, rank_s, crowd_s = e.nsga2_select(torch.from_numpy(xs).to(dev), ns // 2, return_details=True)
+            fin = np.isfinite(w_crowd)
+            crowd_np = crowd_s.cpu().numpy()
+            parity = {"ranks_equal": bool(np.array_equal(rank_s.cpu().numpy(), w_rank)),
+                      "order_equal": bool(np.array_equal(order_s.cpu().numpy(), w_order)),
+                      "crowding_rtol_1e-6": bool(np.array_equal(np.isfinite(crowd_np), fin)
+                                                 and np.allclose(crowd_np[fin], w_crowd[fin], rtol=1e-6, atol=0)),
+                      "checker": f"oracle/nds_oracle.c, {ns} of {n} rows (the cpu_baseline step's own result), after the timed regions"}
 
     line = {
         "metric": METRIC, "value": pairs / (t_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
