@@ -36,17 +36,64 @@ def _register():
     _registered = True
 
 
+def _nds_call(x):
+    return jax.ffi.ffi_call("evoxb_nds", jax.ShapeDtypeStruct((x.shape[0],), jnp.int32))(x)
+
+
+def _crowding_call(costs, mask):
+    return jax.ffi.ffi_call("evoxb_crowding", jax.ShapeDtypeStruct((costs.shape[0],), jnp.float32))(costs, mask)
+
+
+# ---- partitioning rule (jit over a device mesh, e.g. StdWorkflow under `jax.sharding`) -----------------------
+# A custom call is opaque to the SPMD partitioner; without a rule it refuses sharded operands.  The ranking of one
+# population is a whole-population computation, so the rule is the simplest correct one: every operand and the
+# result are REPLICATED (each device ranks the full population, exactly what the reference does today:
+# `tell` runs replicated per device, workflows/std_workflow.py:194,341).  Sharding the matrix by column chunk over
+# the devices is what `evoxb_nds_rank_sharded_f32` does; binding that needs a communicator per process and is the
+# next step after these handlers have been compiled once.  Like the rest of this file: never run here.
+def _replicated(mesh, ndim):
+    from jax.sharding import NamedSharding, PartitionSpec
+
+    return NamedSharding(mesh, PartitionSpec(*([None] * ndim)))
+
+
+def _with_replication_rule(fn, result_ndim):
+    from jax.experimental.custom_partitioning import custom_partitioning
+
+    wrapped = custom_partitioning(fn)
+
+    def infer_sharding_from_operands(mesh, arg_shapes, result_shape):
+        return _replicated(mesh, result_ndim)
+
+    def partition(mesh, arg_shapes, result_shape):
+        arg_shardings = tuple(_replicated(mesh, len(a.shape)) for a in arg_shapes)
+        return mesh, fn, _replicated(mesh, result_ndim), arg_shardings
+
+    wrapped.def_partition(infer_sharding_from_operands=infer_sharding_from_operands, partition=partition)
+    return wrapped
+
+
+_nds_partitioned = None
+_crowding_partitioned = None
+
+
 def non_dominated_sort(x, method="auto"):
-    """Same signature as the reference (non_dominate.py:30-31); traceable under jit / cond / pmap."""
+    """Same signature as the reference (non_dominate.py:30-31); traceable under jit / cond / pmap, and under a
+    sharded jit through the replication rule above."""
+    global _nds_partitioned
     assert method in ["auto", "scan", "full map-reduce", "host"], "method must be either 'auto', 'scan', or 'full map-reduce', 'host'"
     _register()
-    return jax.ffi.ffi_call("evoxb_nds", jax.ShapeDtypeStruct((x.shape[0],), jnp.int32))(x.astype(jnp.float32))
+    if _nds_partitioned is None:
+        _nds_partitioned = _with_replication_rule(_nds_call, 1)
+    return _nds_partitioned(x.astype(jnp.float32))
 
 
 def crowding_distance(costs, mask=None):
     """Same signature as the reference (non_dominate.py:116-117)."""
+    global _crowding_partitioned
     _register()
     if mask is None:
         mask = jnp.ones((costs.shape[0],), dtype=jnp.bool_)
-    return jax.ffi.ffi_call("evoxb_crowding", jax.ShapeDtypeStruct((costs.shape[0],), jnp.float32))(
-        costs.astype(jnp.float32), mask.astype(jnp.bool_))
+    if _crowding_partitioned is None:
+        _crowding_partitioned = _with_replication_rule(_crowding_call, 1)
+    return _crowding_partitioned(costs.astype(jnp.float32), mask.astype(jnp.bool_))
