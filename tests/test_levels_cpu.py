@@ -140,3 +140,27 @@ def test_build_path_host_side_answer(monkeypatch):
     monkeypatch.setenv("EVOXB_BUILD_MODE", "levels")
     _lib.check(L.evoxb_nds_workspace_bytes(65536, 5, ctypes.byref(need_b)))
     assert 0 < need_b.value - need_a.value < (32 << 20)
+
+
+def test_level_map_monotone_on_arbitrary_floats():
+    """Property form of the monotonicity above on arbitrary float32 bit patterns (hypothesis): denormals, both
+    zeros, infinities, NaN (excluded from the order, as in the kernels), huge dynamic range."""
+    hyp = pytest.importorskip("hypothesis")
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+    from hypothesis.extra import numpy as hnp
+
+    @settings(max_examples=60, deadline=None)
+    @given(hnp.arrays(np.uint32, st.integers(2, 400), elements=st.integers(0, 2**32 - 1)))
+    def check(bits):
+        x = bits.view(np.float32)
+        lv, key = levels_of(x)
+        ok = ~np.isnan(x)
+        if ok.sum() < 2:
+            return
+        xs, ls = x[ok], lv[ok].astype(np.int64)
+        le = xs[:, None] <= xs[None, :]
+        assert np.all((ls[:, None] <= ls[None, :])[le])
+        assert ls.max() < LEVELS
+
+    check()
